@@ -1,0 +1,144 @@
+/*
+ * orbb200.h -- C-ABI of liborbb200.so: the B200 (sm_100a) drop-in for ORB-SLAM2's front-end hot path.
+ *
+ * The reference has no FFI/plugin layer for this path: callers instantiate two C++ classes directly
+ * (ORB_SLAM2::ORBextractor, include/ORBextractor.h:53-135; ORB_SLAM2::ORBmatcher, include/ORBmatcher.h:38-100).
+ * This header is the boundary a replacement library exports underneath source-compatible facades of those
+ * classes (include/orbb200/ORBextractor.h, include/orbb200/ORBmatcher.h).  Each entry point cites the
+ * reference interface it replaces as file:line relative to /root/reference.
+ *
+ * Conventions: plain pointers and sizes only.  Pointers are HOST memory unless the name ends in `_d`
+ * (device memory on the handle's GPU).  Every function returns 0 on success, <0 on error; the message is
+ * available from orbb200_last_error() (thread-local).  There is no CPU fallback: without a CUDA device every
+ * compute entry point fails with ORBB200_ERR_CUDA.
+ */
+#ifndef ORBB200_H
+#define ORBB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBB200_OK 0
+#define ORBB200_ERR_ARG (-1)      /* bad argument (null, non-positive size, unsupported shape) */
+#define ORBB200_ERR_CUDA (-2)     /* CUDA runtime error / no device */
+#define ORBB200_ERR_CAPACITY (-3) /* caller's output capacity too small */
+#define ORBB200_ERR_STATE (-4)    /* call order (e.g. pyramid requested before any extract) */
+
+#define ORBB200_MAX_LEVELS 32
+
+/* == cv::KeyPoint layout (7 x 4 bytes): pt.x, pt.y, size, angle, response, octave, class_id */
+typedef struct {
+    float x, y, size, angle, response;
+    int octave, class_id;
+} orbb200_keypoint;
+
+typedef struct orbb200_extractor orbb200_extractor; /* opaque; one CUDA stream + workspace per handle */
+
+/* ---- extractor ------------------------------------------------------------------------------------ */
+
+/* replaces ORBextractor::ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
+ * int minThFAST)  (include/ORBextractor.h:66-67, src/ORBextractor.cc:429-534).  device = -1: current. */
+int orbb200_extractor_create(orbb200_extractor **out, int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
+                             int minThFAST, int device);
+void orbb200_extractor_destroy(orbb200_extractor *e);
+
+/* replaces GetLevels / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares (include/ORBextractor.h:78-98) and exposes mnFeaturesPerLevel (:123).
+ * Any output pointer may be NULL.  Arrays have nlevels entries. */
+int orbb200_level_tables(const orbb200_extractor *e, float *scale, float *inv_scale, float *sigma2, float *inv_sigma2,
+                         int *nfeat);
+
+/* upper bound on keypoints per image for this handle (DistributeOctTree can exceed the per-level quota by
+ * up to 3 nodes: src/ORBextractor.cc:879).  Use it to size kps/desc. */
+int orbb200_max_keypoints(const orbb200_extractor *e);
+
+/* replaces ORBextractor::operator()(image, mask, keypoints, descriptors) (include/ORBextractor.h:74-76,
+ * src/ORBextractor.cc:1261-1339) for one 8-bit single-channel image.  kps[cap], desc[cap*32] are host
+ * buffers; *n_out receives the keypoint count.  An empty image (img NULL or w/h 0) returns OK with
+ * *n_out = 0, like the reference's early return (:1264).  The mask argument of the reference is ignored
+ * there and has no counterpart here. */
+int orbb200_extract(orbb200_extractor *e, const uint8_t *img, int width, int height, int stride,
+                    orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out);
+
+/* the same for `batch` images of one shape (frame-sharded configs); image b's outputs start at
+ * kps + b*cap and desc + b*cap*32; n_out[batch].  Host buffers; H2D/D2H copies are inside the call. */
+int orbb200_extract_batch(orbb200_extractor *e, const uint8_t *const *imgs, int batch, int width, int height,
+                          int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out);
+
+/* device-resident variant: imgs_d holds `batch` images, image b at imgs_d + b*image_stride, rows `stride`
+ * bytes apart; outputs are device buffers laid out as above.  Asynchronous on the handle's stream (see
+ * orbb200_extractor_stream); no host synchronisation inside. */
+int orbb200_extract_batch_device(orbb200_extractor *e, const uint8_t *imgs_d, int batch, int width, int height,
+                                 int stride, size_t image_stride, orbb200_keypoint *kps_d, uint8_t *desc_d, int cap,
+                                 int *n_out_d);
+
+/* replaces reads of the public member mvImagePyramid[level] (include/ORBextractor.h:100; read by
+ * src/Frame.cc:584,674,686,691): copies the UN-blurred level of image `image_index` of the last call
+ * to dst (rows dst_stride apart).  dst may be NULL to query the size only. */
+int orbb200_pyramid_level(orbb200_extractor *e, int image_index, int level, uint8_t *dst, int dst_stride, int *w,
+                          int *h);
+
+/* cudaStream_t of the handle (as void*), so callers can order their own work / events against it. */
+void *orbb200_extractor_stream(orbb200_extractor *e);
+int orbb200_extractor_sync(orbb200_extractor *e);
+
+/* per-stage device time of the LAST extract call, measured with CUDA events on the handle's stream when
+ * profiling is enabled (off by default; the events serialise nothing but add ~1 us per stage).
+ * stages: 0 pyramid, 1 fast_cells, 2 octree_select, 3 blur7, 4 orient_describe.  ms[5]. */
+int orbb200_extractor_set_profiling(orbb200_extractor *e, int on);
+int orbb200_extractor_stage_ms(orbb200_extractor *e, float *ms, int n);
+/* number of kernel launches issued by the last extract call */
+int orbb200_extractor_last_launches(const orbb200_extractor *e);
+
+/* test/debug taps on the last call (image_index within the batch): pre-quadtree candidates of a level in the
+ * reference's vToDistributeKeys order (src/ORBextractor.cc:997-1006), as (x, y, response) int triples with
+ * coordinates relative to the 16-px border; and the blurred level (:1312-1314). */
+int orbb200_debug_candidates(orbb200_extractor *e, int image_index, int level, int *xyr, int cap, int *n);
+int orbb200_debug_blurred_level(orbb200_extractor *e, int image_index, int level, uint8_t *dst, int dst_stride);
+
+/* ---- matcher ---------------------------------------------------------------------------------------- */
+
+/* running best / second-best of ORBmatcher's searches (src/ORBmatcher.cc:214-240): best_idx is the first
+ * candidate attaining best_dist; second_dist counts duplicates; 256 / -1 when absent. */
+typedef struct {
+    int best_dist, best_idx, second_dist, second_idx;
+} orbb200_top2;
+
+/* replaces static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&)
+ * (include/ORBmatcher.h:44, src/ORBmatcher.cc:1733-1749) for arrays of pairs: dist[i] = H(a[i], b[i]). */
+int orbb200_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int *dist, int device);
+
+/* X1 (BASELINE config 5): the best/second-best loop of src/ORBmatcher.cc:214-244 over a flat database. */
+int orbb200_match_bruteforce_top2(const uint8_t *q, int nq, const uint8_t *db, int ndb, orbb200_top2 *out,
+                                  int device);
+int orbb200_match_bruteforce_top2_device(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb,
+                                         orbb200_top2 *out_d, int index_offset, void *stream);
+
+/* M2-M9 core: per-query candidate lists (CSR: cand_offsets[nq+1], cand_idx) visited in list order -- the
+ * inner loops of SearchByProjection (src/ORBmatcher.cc:90-123, 1482-1508), SearchByBoW (:214-240),
+ * SearchForTriangulation (:768-815), Fuse (:960-1003), SearchBySim3 (:1268-1283). */
+int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets,
+                             const int *cand_idx, orbb200_top2 *out, int device);
+
+/* merge of per-shard top-2 results (config 5, database sharded by rows; shard s's indices already global):
+ * parts[s*nq + i]; ties on best_dist go to the lowest shard (= lowest global index, first-seen rule). */
+int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);
+int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream);
+
+/* F1: replaces Frame::ComputeStereoMatches (src/Frame.cc:577-751) using the device-resident pyramids and
+ * outputs of the LAST single-image extract on `left` and `right`.  uRight[nL], depth[nL] host outputs
+ * (-1 where unmatched).  bf = mbf, b = mb (baseline in metres). */
+int orbb200_stereo_match(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight,
+                         float *depth, int *n_valid);
+
+const char *orbb200_last_error(void);
+const char *orbb200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBB200_H */

@@ -1,0 +1,56 @@
+// extractor_host.cuh -- the handle behind orbb200_extractor (one CUDA stream + workspaces per instance;
+// the reference runs two extractor instances concurrently on two host threads, src/Frame.cc:82-85).
+#pragma once
+#include <vector>
+
+#include "extract_kernels.cuh"
+
+struct orbb200_extractor {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    // E1 tables (src/ORBextractor.cc:429-534)
+    int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
+    double scaleFactor = 0;
+    float sf[ORBB200_MAX_LEVELS], isf[ORBB200_MAX_LEVELS], sig2[ORBB200_MAX_LEVELS], isig2[ORBB200_MAX_LEVELS];
+    int nfeat[ORBB200_MAX_LEVELS];
+    int umax[16];
+    // shape-dependent state
+    int w = 0, h = 0, batchCap = 0;
+    orbb200::LevelGeom geom[ORBB200_MAX_LEVELS];
+    size_t pyrStride = 0, candStride = 0, nodeWsStride = 0;
+    int totalCells = 0, nodeTotal = 0, totalBlurTiles = 0, coefTotal = 0;
+    size_t octreeSmem = 0;
+    // device buffers
+    orbb200::LevelGeom *d_geom = nullptr;
+    int *d_umax = nullptr;
+    int *d_rzXofs = nullptr, *d_rzYofs = nullptr;
+    short2 *d_rzXa = nullptr, *d_rzYb = nullptr;
+    uint8_t *d_pyr = nullptr, *d_blur = nullptr;
+    uint32_t *d_cand = nullptr, *d_ord = nullptr, *d_lvlKp = nullptr;
+    int *d_knode = nullptr, *d_cellCount = nullptr, *d_cellScan = nullptr, *d_nodeWs = nullptr, *d_lvlCount = nullptr;
+    // outputs owned by the handle (host API, stereo matcher)
+    orbb200_keypoint *d_kps = nullptr;
+    uint8_t *d_desc = nullptr;
+    int *d_nOut = nullptr;
+    int outCap = 0, outBatch = 0;
+    // last call
+    int lastBatch = 0, lastCap = 0;
+    const uint8_t *lastL0 = nullptr;
+    size_t lastL0ImgStride = 0;
+    int lastL0Pitch = 0;
+    const orbb200_keypoint *lastKps = nullptr;
+    const uint8_t *lastDesc = nullptr;
+    const int *lastNOut = nullptr;
+    int lastLaunches = 0;
+    // profiling
+    int profiling = 0;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool evValid = false;
+};
+
+namespace orbb200 {
+int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch);
+int extractor_ensure_outputs(orbb200_extractor *e, int batch, int cap);
+int extractor_run(orbb200_extractor *e, const uint8_t *l0, size_t l0ImgStride, int l0Pitch, int l0Valid, int batch,
+                  orbb200_keypoint *kps_d, uint8_t *desc_d, int cap, int *nOut_d);
+} // namespace orbb200

@@ -1,0 +1,183 @@
+// orbb200_extract.cu -- C-ABI of the extractor (include/orbb200.h) over the sm_100a kernels.
+// Mirrors ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:53-135, src/ORBextractor.cc).
+#include <math.h>
+#include <stdarg.h>
+
+#include <algorithm>
+#include <new>
+
+#include "describe_kernel.cuh"
+#include "extractor_host.cuh"
+#include "octree_kernel.cuh"
+
+namespace orbb200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+
+template <typename T> static int dev_alloc(T **p, size_t count)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    ORB_CUDA_OK(cudaMalloc((void **)p, std::max<size_t>(count, 1) * sizeof(T)));
+    return ORBB200_OK;
+}
+
+static short sat_short(int v) { return (short)std::min(32767, std::max(-32768, v)); }
+
+// Per-shape geometry: pyramid sizes (:1351-1353), 30-px cell grid (:934-951), quadtree roots (:627-629),
+// cv::resize coefficient tables, workspace offsets.
+int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
+{
+    const bool sameShape = (w == e->w && h == e->h);
+    if (sameShape && batch <= e->batchCap) return ORBB200_OK;
+    ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
+    const int L = e->nlevels;
+    if (!sameShape) {
+        size_t imgOff = 0, candOff = 0, wsOff = 0;
+        int cellBase = 0, nodeOff = 0, tileBase = 0, coefOff = 0;
+        size_t octSmem = 0;
+        for (int l = 0; l < L; l++) {
+            LevelGeom &g = e->geom[l];
+            memset(&g, 0, sizeof(g));
+            g.w = cv_round_f((float)w * e->isf[l]);
+            g.h = cv_round_f((float)h * e->isf[l]);
+            if (g.w < 1 || g.h < 1) { set_error("level %d of a %dx%d image is empty", l, w, h); return ORBB200_ERR_ARG; }
+            if (g.w > 4127 || g.h > 4127) { set_error("level %d (%dx%d) exceeds the 12-bit candidate packing", l, g.w, g.h); return ORBB200_ERR_ARG; }
+            g.pitch = (int)align_up(g.w, 16);
+            g.imgOff = (unsigned int)imgOff;
+            imgOff += align_up((size_t)g.pitch * g.h, 256);
+            const float width = (float)(g.w - 32), height = (float)(g.h - 32);
+            g.nCols = width > 0 ? (int)(width / 30.f) : 0;
+            g.nRows = height > 0 ? (int)(height / 30.f) : 0;
+            if (g.nCols < 1 || g.nRows < 1) { g.nCols = g.nRows = 0; g.wCell = g.hCell = 1; }
+            else { g.wCell = (int)ceilf(width / g.nCols); g.hCell = (int)ceilf(height / g.nRows); }
+            g.cellBase = cellBase;
+            g.nCells = g.nCols * g.nRows;
+            cellBase += g.nCells;
+            g.cellCap = ((g.wCell + 1) / 2) * ((g.hCell + 1) / 2);
+            g.candOff = (unsigned int)candOff;
+            g.candCap = g.nCells * g.cellCap;
+            if (g.candCap > (1 << 21) - 1) { set_error("level %d: candidate capacity %d exceeds 2^21", l, g.candCap); return ORBB200_ERR_ARG; }
+            candOff += align_up((size_t)g.candCap, 64);
+            g.nfeat = e->nfeat[l];
+            int nIni = 1;
+            if (width > 0 && height > 0) nIni = (int)roundf(width / (g.h - 32));
+            if (nIni < 1) nIni = 1; // the reference divides by zero for portrait images (:627-628)
+            g.nIni = nIni;
+            g.hX = width > 0 ? width / nIni : 1.f;
+            g.nodeCap = std::max(g.nfeat + 3, 4 * nIni) + 8;
+            g.sortLen = 1;
+            while (g.sortLen < g.nodeCap) g.sortLen <<= 1;
+            g.nodeOff = nodeOff;
+            nodeOff += g.nodeCap;
+            g.nodeWsOff = (unsigned int)wsOff;
+            wsOff += align_up((size_t)21 * g.nodeCap, 32);
+            octSmem = std::max(octSmem, align_up((size_t)16 * g.nodeCap, 16) + (size_t)8 * g.sortLen);
+            g.scale = e->sf[l];
+            g.patch = (float)(int)(31 * e->sf[l]); // scaledPatchSize (:1023)
+            g.blurTileBase = tileBase;
+            g.blurTilesX = div_up(g.w, BL_TW);
+            g.blurTilesY = div_up(g.h, BL_TH);
+            tileBase += g.blurTilesX * g.blurTilesY;
+            g.coefOff = (unsigned int)coefOff;
+            coefOff += (int)align_up(std::max(g.w, g.h), 4);
+        }
+        e->pyrStride = imgOff;
+        e->candStride = candOff;
+        e->nodeWsStride = wsOff;
+        e->totalCells = cellBase;
+        e->nodeTotal = nodeOff;
+        e->totalBlurTiles = tileBase;
+        e->coefTotal = coefOff;
+        e->octreeSmem = octSmem;
+        if (octSmem > 200 * 1024) { set_error("nfeatures too large for the quadtree kernel's shared memory (%zu B)", octSmem); return ORBB200_ERR_ARG; }
+        // cv::resize INTER_LINEAR tables (scale = 1/((double)dst/src), 11-bit coefficients)
+        std::vector<int> xofs(coefOff, 0), yofs(coefOff, 0);
+        std::vector<short2> xa(coefOff, make_short2(0, 0)), yb(coefOff, make_short2(0, 0));
+        for (int l = 1; l < L; l++) {
+            LevelGeom &g = e->geom[l];
+            const LevelGeom &s = e->geom[l - 1];
+            const double scale_x = 1. / ((double)g.w / s.w), scale_y = 1. / ((double)g.h / s.h);
+            for (int dx = 0; dx < g.w; dx++) {
+                float fx = (float)((dx + 0.5) * scale_x - 0.5);
+                int sx = (int)floorf(fx);
+                fx -= sx;
+                if (sx < 0) { fx = 0; sx = 0; }
+                if (sx >= s.w - 1) { fx = 0; sx = s.w - 1; }
+                xofs[g.coefOff + dx] = sx;
+                xa[g.coefOff + dx] = make_short2(sat_short(cv_round_f((1.f - fx) * 2048.f)), sat_short(cv_round_f(fx * 2048.f)));
+            }
+            for (int dy = 0; dy < g.h; dy++) {
+                float fy = (float)((dy + 0.5) * scale_y - 0.5);
+                int sy = (int)floorf(fy);
+                fy -= sy;
+                yofs[g.coefOff + dy] = sy;
+                yb[g.coefOff + dy] = make_short2(sat_short(cv_round_f((1.f - fy) * 2048.f)), sat_short(cv_round_f(fy * 2048.f)));
+            }
+            int maxBytes = 16, maxRows = 1;
+            for (int x0 = 0; x0 < g.w; x0 += RZ_TW) {
+                const int x1 = std::min(x0 + RZ_TW, g.w) - 1;
+                const int xb = xofs[g.coefOff + x0] & ~15;
+                const int last = std::min(xofs[g.coefOff + x1] + 1, s.w - 1);
+                maxBytes = std::max(maxBytes, (int)align_up(last - xb + 1, 16));
+            }
+            for (int y0 = 0; y0 < g.h; y0 += RZ_TH) {
+                const int y1 = std::min(y0 + RZ_TH, g.h) - 1;
+                const int r0 = std::min(std::max(yofs[g.coefOff + y0], 0), s.h - 1);
+                const int r1 = std::min(std::max(yofs[g.coefOff + y1] + 1, 0), s.h - 1);
+                maxRows = std::max(maxRows, r1 - r0 + 1);
+            }
+            g.rzTileSP = maxBytes;
+            g.rzTileRows = maxRows;
+            if ((size_t)maxBytes * maxRows > 160 * 1024) { set_error("scale factor too large for the resize tile"); return ORBB200_ERR_ARG; }
+        }
+        if (dev_alloc(&e->d_geom, L)) return ORBB200_ERR_CUDA;
+        if (dev_alloc(&e->d_rzXofs, coefOff) || dev_alloc(&e->d_rzYofs, coefOff) || dev_alloc(&e->d_rzXa, coefOff) ||
+            dev_alloc(&e->d_rzYb, coefOff))
+            return ORBB200_ERR_CUDA;
+        ORB_CUDA_OK(cudaMemcpy(e->d_geom, e->geom, sizeof(LevelGeom) * L, cudaMemcpyHostToDevice));
+        if (coefOff > 0) {
+            ORB_CUDA_OK(cudaMemcpy(e->d_rzXofs, xofs.data(), sizeof(int) * coefOff, cudaMemcpyHostToDevice));
+            ORB_CUDA_OK(cudaMemcpy(e->d_rzYofs, yofs.data(), sizeof(int) * coefOff, cudaMemcpyHostToDevice));
+            ORB_CUDA_OK(cudaMemcpy(e->d_rzXa, xa.data(), sizeof(short2) * coefOff, cudaMemcpyHostToDevice));
+            ORB_CUDA_OK(cudaMemcpy(e->d_rzYb, yb.data(), sizeof(short2) * coefOff, cudaMemcpyHostToDevice));
+        }
+        e->w = w;
+        e->h = h;
+        e->batchCap = 0;
+    }
+    const size_t B = (size_t)batch;
+    if (dev_alloc(&e->d_pyr, e->pyrStride * B + 256) || dev_alloc(&e->d_blur, e->pyrStride * B + 256) ||
+        dev_alloc(&e->d_cand, e->candStride * B) || dev_alloc(&e->d_ord, e->candStride * B) ||
+        dev_alloc(&e->d_knode, e->candStride * B) || dev_alloc(&e->d_cellCount, (size_t)e->totalCells * B) ||
+        dev_alloc(&e->d_cellScan, (size_t)e->totalCells * B) || dev_alloc(&e->d_nodeWs, e->nodeWsStride * B) ||
+        dev_alloc(&e->d_lvlKp, (size_t)e->nodeTotal * B) || dev_alloc(&e->d_lvlCount, (size_t)L * B))
+        return ORBB200_ERR_CUDA;
+    e->batchCap = batch;
+    return ORBB200_OK;
+}
+
+int extractor_ensure_outputs(orbb200_extractor *e, int batch, int cap)
+{
+    if (batch <= e->outBatch && cap <= e->outCap) return ORBB200_OK;
+    ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
+    const int nb = std::max(batch, e->outBatch), nc = std::max(cap, e->outCap);
+    if (dev_alloc(&e->d_kps, (size_t)nb * nc) || dev_alloc(&e->d_desc, (size_t)nb * nc * 32) || dev_alloc(&e->d_nOut, nb))
+        return ORBB200_ERR_CUDA;
+    e->outBatch = nb;
+    e->outCap = nc;
+    return ORBB200_OK;
+}
+
+} // namespace orbb200
+
+#include "extractor_api.inc"

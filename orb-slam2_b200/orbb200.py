@@ -1,0 +1,259 @@
+"""ctypes binding of liborbb200.so (include/orbb200.h) for the tests and bench.py.
+
+The host-side product is C++ (include/orbb200/ORBextractor.h, ORBmatcher.h); this module only lets the
+Python harness drive the same C-ABI.  Names mirror the reference classes (ORBextractor, ORBmatcher).
+There is NO fallback: if the shared library is missing or CUDA is unavailable every call raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liborbb200.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
+
+EXPORTS = [
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_max_keypoints",
+    "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
+    "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling",
+    "orbb200_extractor_stage_ms", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
+    "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
+    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_merge_top2",
+    "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_last_error", "orbb200_version",
+]
+
+_lib = None
+
+
+class OrbB200Error(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OrbB200Error("liborbb200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                           "there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, ip, fp, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    L.orbb200_last_error.restype = C.c_char_p
+    L.orbb200_version.restype = C.c_char_p
+    L.orbb200_extractor_create.argtypes = [C.POINTER(vp), ip, fp, ip, ip, ip, ip]
+    L.orbb200_extractor_destroy.argtypes = [vp]
+    L.orbb200_extractor_destroy.restype = None
+    L.orbb200_level_tables.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbb200_max_keypoints.argtypes = [vp]
+    L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
+    L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]
+    L.orbb200_extract_batch_device.argtypes = [vp, vp, ip, ip, ip, ip, sz, vp, vp, ip, vp]
+    L.orbb200_pyramid_level.argtypes = [vp, ip, ip, vp, ip, vp, vp]
+    L.orbb200_extractor_stream.argtypes = [vp]
+    L.orbb200_extractor_stream.restype = vp
+    L.orbb200_extractor_sync.argtypes = [vp]
+    L.orbb200_extractor_set_profiling.argtypes = [vp, ip]
+    L.orbb200_extractor_stage_ms.argtypes = [vp, vp, ip]
+    L.orbb200_extractor_last_launches.argtypes = [vp]
+    L.orbb200_debug_candidates.argtypes = [vp, ip, ip, vp, ip, vp]
+    L.orbb200_debug_blurred_level.argtypes = [vp, ip, ip, vp, ip]
+    L.orbb200_descriptor_distance.argtypes = [vp, vp, ip, vp, ip]
+    L.orbb200_match_bruteforce_top2.argtypes = [vp, ip, vp, ip, vp, ip]
+    L.orbb200_match_bruteforce_top2_device.argtypes = [vp, ip, vp, ip, vp, ip, vp]
+    L.orbb200_match_candidates.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
+    L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
+    L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
+    L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise OrbB200Error("orbb200 error %d: %s" % (rc, lib().orbb200_last_error().decode()))
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class ORBextractor:
+    """Same constructor and accessors as ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:66-100)."""
+
+    STAGES = ("pyramid", "fast_cells", "octree_select", "blur7", "orient_describe")
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device=-1):
+        self.L = lib()
+        h = C.c_void_p()
+        check(self.L.orbb200_extractor_create(C.byref(h), nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device))
+        self.h = h
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self.cap = self.L.orbb200_max_keypoints(self.h)
+        n = nlevels
+        self._t = [np.zeros(n, np.float32) for _ in range(4)] + [np.zeros(n, np.int32)]
+        check(self.L.orbb200_level_tables(self.h, *[_p(a) for a in self._t]))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.orbb200_extractor_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # accessors (reference ORBextractor.h:78-98)
+    def GetLevels(self):
+        return self.nlevels
+
+    def GetScaleFactors(self):
+        return self._t[0].copy()
+
+    def GetInverseScaleFactors(self):
+        return self._t[1].copy()
+
+    def GetScaleSigmaSquares(self):
+        return self._t[2].copy()
+
+    def GetInverseScaleSigmaSquares(self):
+        return self._t[3].copy()
+
+    def GetFeaturesPerLevel(self):
+        return self._t[4].copy()
+
+    def __call__(self, image):
+        """operator()(image, mask, keypoints, descriptors): returns (keypoints[KP_DTYPE], descriptors[N,32])."""
+        if image is None or image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 required (reference :1269)"
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int(0)
+        check(self.L.orbb200_extract(self.h, _p(image), w, h, image.strides[0], _p(kps), _p(desc), self.cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, images, kps=None, desc=None, n_out=None):
+        """images: [B,H,W] uint8 (host).  Returns (kps[B,cap], desc[B,cap,32], n[B])."""
+        images = np.ascontiguousarray(images, np.uint8) if not isinstance(images, np.ndarray) else images
+        B, h, w = images.shape
+        stride = images.strides[1]
+        ptrs = (C.c_void_p * B)(*[images.ctypes.data + b * images.strides[0] for b in range(B)])
+        if kps is None:
+            kps = np.zeros((B, self.cap), KP_DTYPE)
+            desc = np.zeros((B, self.cap, 32), np.uint8)
+            n_out = np.zeros(B, np.int32)
+        check(self.L.orbb200_extract_batch(self.h, ptrs, B, w, h, stride, _p(kps), _p(desc), self.cap, _p(n_out)))
+        return kps, desc, n_out
+
+    def extract_batch_device(self, imgs_ptr, batch, width, height, stride, image_stride, kps_ptr, desc_ptr, cap, n_ptr):
+        check(self.L.orbb200_extract_batch_device(self.h, imgs_ptr, batch, width, height, stride, image_stride,
+                                                  kps_ptr, desc_ptr, cap, n_ptr))
+
+    def stream(self):
+        return self.L.orbb200_extractor_stream(self.h)
+
+    def sync(self):
+        check(self.L.orbb200_extractor_sync(self.h))
+
+    def set_profiling(self, on):
+        check(self.L.orbb200_extractor_set_profiling(self.h, int(on)))
+
+    def stage_ms(self):
+        ms = np.zeros(5, np.float32)
+        check(self.L.orbb200_extractor_stage_ms(self.h, _p(ms), 5))
+        return dict(zip(self.STAGES, ms.tolist()))
+
+    def last_launches(self):
+        return self.L.orbb200_extractor_last_launches(self.h)
+
+    def pyramid_level(self, level, image_index=0):
+        """mvImagePyramid[level] (un-blurred) of the last call."""
+        w, h = C.c_int(), C.c_int()
+        check(self.L.orbb200_pyramid_level(self.h, image_index, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        check(self.L.orbb200_pyramid_level(self.h, image_index, level, _p(out), w.value, C.byref(w), C.byref(h)))
+        return out
+
+    def debug_blurred_level(self, level, image_index=0):
+        w, h = C.c_int(), C.c_int()
+        check(self.L.orbb200_pyramid_level(self.h, image_index, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        check(self.L.orbb200_debug_blurred_level(self.h, image_index, level, _p(out), w.value))
+        return out
+
+    def debug_candidates(self, level, image_index=0):
+        n = C.c_int()
+        check(self.L.orbb200_debug_candidates(self.h, image_index, level, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 3), np.int32)
+        check(self.L.orbb200_debug_candidates(self.h, image_index, level, _p(out), n.value, C.byref(n)))
+        return out[:n.value]
+
+
+class ORBmatcher:
+    """Descriptor-distance searches of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:38-100) on POD arrays."""
+    TH_HIGH = 100
+    TH_LOW = 50
+    HISTO_LENGTH = 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=-1):
+        self.L = lib()
+        self.mfNNratio = np.float32(nnratio)
+        self.mbCheckOrientation = checkOri
+        self.device = device
+
+    def DescriptorDistance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+        b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        out = np.zeros(len(a), np.int32)
+        check(self.L.orbb200_descriptor_distance(_p(a), _p(b), len(a), _p(out), self.device))
+        return out
+
+    def bruteforce_top2(self, q, db):
+        q = np.ascontiguousarray(q, np.uint8)
+        db = np.ascontiguousarray(db, np.uint8)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        check(self.L.orbb200_match_bruteforce_top2(_p(q), len(q), _p(db), len(db), _p(out), self.device))
+        return out
+
+    def match_candidates(self, q, t, offsets, idx):
+        q = np.ascontiguousarray(q, np.uint8)
+        t = np.ascontiguousarray(t, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        idx = np.ascontiguousarray(idx, np.int32)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        check(self.L.orbb200_match_candidates(_p(q), len(q), _p(t), len(t), _p(offsets), _p(idx), _p(out), self.device))
+        return out
+
+    def merge_top2(self, parts):
+        parts = np.ascontiguousarray(parts, TOP2_DTYPE)
+        ns, nq = parts.shape
+        out = np.zeros(nq, TOP2_DTYPE)
+        check(self.L.orbb200_merge_top2(_p(parts), ns, nq, _p(out), self.device))
+        return out
+
+    def accept_ratio(self, top2, th=None):
+        """best <= th and best < ratio*second (reference ORBmatcher.cc:242-244), f32 compare."""
+        th = self.TH_LOW if th is None else th
+        b = top2["best_dist"].astype(np.float32)
+        s = top2["second_dist"].astype(np.float32)
+        return (top2["best_dist"] <= th) & (b < self.mfNNratio * s)
+
+
+def stereo_match(left, right, bf, b):
+    """Frame::ComputeStereoMatches on the device-resident results of the last single-image extract of both handles."""
+    n = left.cap
+    uR = np.zeros(n, np.float32)
+    depth = np.zeros(n, np.float32)
+    nv = C.c_int()
+    check(lib().orbb200_stereo_match(left.h, right.h, bf, b, _p(uR), _p(depth), C.byref(nv)))
+    return uR, depth, nv.value
