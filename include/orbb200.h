@@ -135,6 +135,10 @@ int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, 
 int orbb200_stereo_match(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight,
                          float *depth, int *n_valid);
 
+/* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
+ * roofline; runs a dependent-free popc microkernel for a few milliseconds. */
+int orbb200_popc_peak(int device, double *popc32_per_s);
+
 const char *orbb200_last_error(void);
 const char *orbb200_version(void);
 

@@ -919,7 +919,7 @@ int ref_stereo_match(const ref_keypoint *kL, const uint8_t *dL, int nL, const re
             float bestuR = sf[levelL] * ((float)scaleduR0 + (float)bestinc + deltaR);
             float disparity = uL - bestuR;
             if (disparity >= minD && disparity < maxD) {
-                if (disparity <= 0) { disparity = 0.01f; bestuR = uL - 0.01f; }
+                if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); } /* double literal (:725) */
                 depth[iL] = bf / disparity;
                 uRight[iL] = bestuR;
                 vd[nvd].dist = best; vd[nvd].idx = iL; nvd++;

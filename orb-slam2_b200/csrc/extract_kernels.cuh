@@ -59,6 +59,8 @@ struct ExtractParams {
     int *nOut;
 };
 
+#ifdef ORBB200_EXTRACT_IMPL // kernel definitions: only orbb200_extract.cu instantiates them
+
 __device__ __forceinline__ const uint8_t *level_ptr(const ExtractParams &P, const LevelGeom &g, int l, int b,
                                                     int &pitch, int &valid)
 {
@@ -374,5 +376,7 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
     }
     if (threadIdx.x == 0) *cellCount = total;
 }
+
+#endif // ORBB200_EXTRACT_IMPL
 
 } // namespace orbb200

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <new>
 
+#define ORBB200_EXTRACT_IMPL
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
 #include "octree_kernel.cuh"

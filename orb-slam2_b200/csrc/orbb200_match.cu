@@ -1,2 +1,223 @@
-// placeholder until the matcher kernels land
-#include "common.cuh"
+// orbb200_match.cu -- C-ABI of the matcher searches (include/orbb200.h) over match_kernels.cuh / stereo_kernel.cuh.
+// Mirrors the arithmetic of ORB_SLAM2::ORBmatcher (reference src/ORBmatcher.cc) on POD arrays; the
+// MapPoint / KeyFrame bookkeeping of the Search* methods stays in the C++ facade (include/orbb200/ORBmatcher.h).
+#include <algorithm>
+
+#include "extractor_host.cuh"
+#include "match_kernels.cuh"
+#include "stereo_kernel.cuh"
+
+namespace orbb200 {
+
+// grow-only per-thread device scratch, so the host-buffer entry points do not cudaMalloc on every call
+struct Scratch {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    void *buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t cap[6] = {0, 0, 0, 0, 0, 0};
+};
+static thread_local Scratch g_scratch;
+
+static int scratch_bind(int device)
+{
+    if (device < 0) ORB_CUDA_OK(cudaGetDevice(&device));
+    ORB_CUDA_OK(cudaSetDevice(device));
+    Scratch &s = g_scratch;
+    if (s.device != device) {
+        for (int i = 0; i < 6; i++) { s.buf[i] = nullptr; s.cap[i] = 0; } // buffers of another device are leaked on purpose
+        s.stream = nullptr;
+        s.device = device;
+    }
+    if (!s.stream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    return ORBB200_OK;
+}
+
+static int scratch_get(int slot, size_t bytes, void **out)
+{
+    Scratch &s = g_scratch;
+    if (s.cap[slot] < bytes) {
+        if (s.buf[slot]) { ORB_CUDA_OK(cudaStreamSynchronize(s.stream)); cudaFree(s.buf[slot]); s.buf[slot] = nullptr; s.cap[slot] = 0; }
+        const size_t nb = std::max<size_t>(align_up(bytes, 256), 4096);
+        ORB_CUDA_OK(cudaMalloc(&s.buf[slot], nb));
+        s.cap[slot] = nb;
+    }
+    *out = s.buf[slot];
+    return ORBB200_OK;
+}
+
+// chunking of the database so that the grid is about 4 blocks per SM on 148 SMs
+static void bf_plan(int nq, int ndb, int *groups, int *chunks, int *rowsPerChunk)
+{
+    *groups = div_up(nq, BF_THREADS * BF_QPT);
+    int c = std::max(1, (148 * 4) / *groups);
+    c = std::min(c, div_up(ndb, BF_TILE));
+    int rows = div_up(ndb, c);
+    rows = div_up(rows, BF_TILE) * BF_TILE;
+    *rowsPerChunk = rows;
+    *chunks = div_up(ndb, rows);
+}
+
+static int bf_launch(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, orbb200_top2 *out_d, int indexOffset,
+                     cudaStream_t st)
+{
+    int groups, chunks, rows;
+    bf_plan(nq, ndb, &groups, &chunks, &rows);
+    void *partial;
+    int rc = scratch_get(5, sizeof(orbb200_top2) * (size_t)chunks * nq, &partial);
+    if (rc) return rc;
+    k_bf_top2<<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb, rows, indexOffset, (orbb200_top2 *)partial);
+    k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>((const orbb200_top2 *)partial, chunks, nq, out_d);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
+}
+
+} // namespace orbb200
+
+#include "stereo_host.inc"
+
+using namespace orbb200;
+
+extern "C" {
+
+int orbb200_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int *dist, int device)
+{
+    if (n <= 0) return ORBB200_OK;
+    ORB_ARG_OK(a && b && dist, "null pointer");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *da, *db, *dd;
+    if ((rc = scratch_get(0, (size_t)n * 32, &da)) || (rc = scratch_get(1, (size_t)n * 32, &db)) ||
+        (rc = scratch_get(2, (size_t)n * 4, &dd)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(da, a, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(db, b, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    k_pair_distance<<<div_up(n, 256), 256, 0, st>>>((const uint8_t *)da, (const uint8_t *)db, n, (int *)dd);
+    ORB_CUDA_OK(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_match_bruteforce_top2_device(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, orbb200_top2 *out_d,
+                                         int index_offset, void *stream)
+{
+    ORB_ARG_OK(q_d && db_d && out_d && nq > 0 && ndb > 0, "bad arguments");
+    ORB_ARG_OK(((size_t)q_d & 15) == 0 && ((size_t)db_d & 15) == 0, "descriptor arrays must be 16-byte aligned");
+    int rc = scratch_bind(-1);
+    if (rc) return rc;
+    return bf_launch(q_d, nq, db_d, ndb, out_d, index_offset, stream ? (cudaStream_t)stream : g_scratch.stream);
+}
+
+int orbb200_match_bruteforce_top2(const uint8_t *q, int nq, const uint8_t *db, int ndb, orbb200_top2 *out, int device)
+{
+    if (nq <= 0) return ORBB200_OK;
+    ORB_ARG_OK(q && out && (db || ndb == 0), "null pointer");
+    if (ndb <= 0) {
+        for (int i = 0; i < nq; i++) out[i] = orbb200_top2{256, -1, 256, -1};
+        return ORBB200_OK;
+    }
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dq, *ddb, *dout;
+    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)ndb * 32, &ddb)) ||
+        (rc = scratch_get(2, (size_t)nq * sizeof(orbb200_top2), &dout)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(ddb, db, (size_t)ndb * 32, cudaMemcpyHostToDevice, st));
+    rc = bf_launch((const uint8_t *)dq, nq, (const uint8_t *)ddb, ndb, (orbb200_top2 *)dout, 0, st);
+    if (rc) return rc;
+    ORB_CUDA_OK(cudaMemcpyAsync(out, dout, (size_t)nq * sizeof(orbb200_top2), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets, const int *cand_idx,
+                             orbb200_top2 *out, int device)
+{
+    if (nq <= 0) return ORBB200_OK;
+    ORB_ARG_OK(q && cand_offsets && out, "null pointer");
+    const int total = cand_offsets[nq];
+    ORB_ARG_OK(total == 0 || (t && cand_idx && nt > 0), "candidates without targets");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dq, *dt, *dout, *doffs, *didx;
+    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)std::max(nt, 1) * 32, &dt)) ||
+        (rc = scratch_get(2, (size_t)nq * sizeof(orbb200_top2), &dout)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
+        (rc = scratch_get(4, (size_t)std::max(total, 1) * 4, &didx)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    if (nt > 0) ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (total > 0) ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
+    k_match_candidates<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
+                                                            (const int *)didx, (orbb200_top2 *)dout);
+    ORB_CUDA_OK(cudaMemcpyAsync(out, dout, (size_t)nq * sizeof(orbb200_top2), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream)
+{
+    ORB_ARG_OK(parts_d && out_d && nshards > 0 && nq > 0, "bad arguments");
+    int rc = scratch_bind(-1);
+    if (rc) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_scratch.stream;
+    k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>(parts_d, nshards, nq, out_d);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
+}
+
+int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device)
+{
+    if (nq <= 0) return ORBB200_OK;
+    ORB_ARG_OK(parts && out && nshards > 0, "bad arguments");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dp, *dout;
+    const size_t nb = sizeof(orbb200_top2) * (size_t)nshards * nq;
+    if ((rc = scratch_get(0, nb, &dp)) || (rc = scratch_get(2, sizeof(orbb200_top2) * (size_t)nq, &dout))) return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dp, parts, nb, cudaMemcpyHostToDevice, st));
+    k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>((const orbb200_top2 *)dp, nshards, nq, (orbb200_top2 *)dout);
+    ORB_CUDA_OK(cudaMemcpyAsync(out, dout, sizeof(orbb200_top2) * (size_t)nq, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_popc_peak(int device, double *popc32_per_s)
+{
+    ORB_ARG_OK(popc32_per_s != nullptr, "null pointer");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *d;
+    if ((rc = scratch_get(2, 256, &d))) return rc;
+    cudaStream_t st = g_scratch.stream;
+    cudaEvent_t e0, e1;
+    ORB_CUDA_OK(cudaEventCreate(&e0));
+    ORB_CUDA_OK(cudaEventCreate(&e1));
+    const int blocks = 148 * 8, threads = 256, iters = 4096;
+    double best = 0;
+    for (int rep = 0; rep < 5; rep++) {
+        ORB_CUDA_OK(cudaEventRecord(e0, st));
+        k_popc_peak<<<blocks, threads, 0, st>>>((unsigned int *)d, iters);
+        ORB_CUDA_OK(cudaEventRecord(e1, st));
+        ORB_CUDA_OK(cudaEventSynchronize(e1));
+        float ms = 0;
+        ORB_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms > 0) best = std::max(best, (double)blocks * threads * iters * 8.0 / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *popc32_per_s = best;
+    return ORBB200_OK;
+}
+
+int orbb200_stereo_match(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight, float *depth,
+                         int *n_valid)
+{
+    return stereo_match_impl(left, right, bf, b, uRight, depth, n_valid);
+}
+
+} // extern "C"

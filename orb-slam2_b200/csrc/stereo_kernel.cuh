@@ -1,0 +1,173 @@
+// stereo_kernel.cuh -- F1: Frame::ComputeStereoMatches (src/Frame.cc:577-751) on the device-resident outputs and
+// pyramids of a left and a right extractor handle.
+//   k_stereo_match   one warp per left keypoint: lanes stride the right keypoints in index order (the row-band
+//                    lists of :594-604 hold right indices in increasing order, so the first-wins arg-min of
+//                    :639-660 is the lexicographic (distance, iR) minimum); then 11 SAD windows of 11x11 on the
+//                    un-blurred level (:672-703), parabola refinement (:709-716) and the disparity gate (:719-733).
+//   k_stereo_median  one block: median of the SAD distances and the 1.5*1.4*median outlier cut (:737-750).
+#pragma once
+#include "extractor_host.cuh"
+#include "match_kernels.cuh"
+
+namespace orbb200 {
+
+struct StereoSide {
+    const orbb200_keypoint *kps;
+    const uint8_t *desc;
+    const int *n;
+    const uint8_t *l0;
+    int l0Pitch;
+    const uint8_t *pyr;
+};
+
+struct StereoParams {
+    StereoSide L, R;
+    const LevelGeom *geom;
+    int nlevels, nRows;
+    float bf, b;
+    float sf[ORBB200_MAX_LEVELS], isf[ORBB200_MAX_LEVELS];
+    float *uRight, *depth;
+    int *sad; // SAD distance per left keypoint, -1 when no depth
+};
+
+__device__ __forceinline__ const uint8_t *stereo_level(const StereoSide &s, const LevelGeom &g, int l, int &pitch)
+{
+    if (l == 0) { pitch = s.l0Pitch; return s.l0; }
+    pitch = g.pitch;
+    return s.pyr + g.imgOff;
+}
+
+__global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ StereoParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nL = *P.L.n, nR = *P.R.n;
+    if (iL >= nL) return;
+    const orbb200_keypoint kL = P.L.kps[iL];
+    float uRight = -1.f, depth = -1.f;
+    int sadOut = -1;
+    const int levelL = kL.octave;
+    const float vL = kL.y, uL = kL.x;
+    const int row = (int)vL;
+    const float maxD = __fdiv_rn(P.bf, P.b);
+    const float minU = __fsub_rn(uL, maxD), maxU = uL;
+    Top2 t;
+    top2_init(t);
+    t.d1 = 100; // bestDist starts at TH_HIGH (:633)
+    if (row >= 0 && row < P.nRows && !(maxU < 0)) {
+        const Desc dL = load_desc(P.L.desc + (size_t)iL * 32);
+        for (int iR = lane; iR < nR; iR += 32) {
+            const orbb200_keypoint kR = P.R.kps[iR];
+            const float r = __fmul_rn(2.0f, P.sf[kR.octave]);
+            const int maxr = (int)ceilf(__fadd_rn(kR.y, r)), minr = (int)floorf(__fsub_rn(kR.y, r));
+            if (row < minr || row > maxr) continue;
+            if (kR.octave < levelL - 1 || kR.octave > levelL + 1) continue;
+            if (kR.x >= minU && kR.x <= maxU) {
+                const int d = hamming(dL, load_desc(P.R.desc + (size_t)iR * 32));
+                if (d < t.d1) { t.d1 = d; t.i1 = iR; }
+            }
+        }
+    }
+    // warp arg-min under (distance, iR)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const int od = __shfl_xor_sync(0xffffffffu, t.d1, o), oi = __shfl_xor_sync(0xffffffffu, t.i1, o);
+        if (lex_less(od, oi, t.d1, t.i1)) { t.d1 = od; t.i1 = oi; }
+    }
+    if (t.i1 >= 0 && t.d1 < 75) { // thOrbDist = (TH_HIGH+TH_LOW)/2 (:582,663)
+        const float uR0 = P.R.kps[t.i1].x;
+        const float scaleFactor = P.isf[levelL];
+        const float scaleduL = roundf(__fmul_rn(uL, scaleFactor)), scaledvL = roundf(__fmul_rn(vL, scaleFactor));
+        const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
+        const LevelGeom g = P.geom[levelL];
+        const int W = g.w, H = g.h;
+        const int cy = (int)scaledvL, cxl = (int)scaleduL, cxr = (int)scaleduR0;
+        const float iniu = scaleduR0, endu = __fadd_rn(scaleduR0, 11.f);
+        const bool inRef = !(iniu < 0 || endu >= (float)W);
+        const bool inImg = !(cy - 5 < 0 || cy + 5 >= H || cxl - 5 < 0 || cxl + 5 >= W || cxr - 10 < 0 || cxr + 10 >= W);
+        if (inRef && inImg) {
+            int pl, pr;
+            const uint8_t *IL = stereo_level(P.L, g, levelL, pl), *IR = stereo_level(P.R, g, levelL, pr);
+            const int lc = IL[(size_t)cy * pl + cxl];
+            // each lane owns up to 4 of the 121 patch pixels; its left values are inc-independent
+            int lv[4], off[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int p = lane + 32 * k;
+                const int dy = p / 11 - 5, dx = p % 11 - 5;
+                lv[k] = p < 121 ? (int)IL[(size_t)(cy + dy) * pl + cxl + dx] - lc : 0;
+                off[k] = p < 121 ? (cy + dy) * pr + cxr + dx : -1;
+            }
+            int best = 0x7fffffff, bestinc = 0, dists[11];
+#pragma unroll
+            for (int inc = -5; inc <= 5; inc++) {
+                const int rc = IR[(size_t)cy * pr + cxr + inc];
+                int s = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (off[k] >= 0) s += abs(lv[k] - ((int)IR[off[k] + inc] - rc));
+                s = warp_sum(s);
+                dists[inc + 5] = s;
+                if (s < best) { best = s; bestinc = inc; }
+            }
+            if (bestinc != -5 && bestinc != 5) {
+                float d1 = 0, d2 = 0, d3 = 0;
+#pragma unroll
+                for (int k = 1; k < 10; k++)
+                    if (k == bestinc + 5) { d1 = (float)dists[k - 1]; d2 = (float)dists[k]; d3 = (float)dists[k + 1]; }
+                const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                if (!(deltaR < -1 || deltaR > 1)) {
+                    float bestuR = __fmul_rn(P.sf[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= 0 && disparity < maxD) {
+                        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+                        depth = __fdiv_rn(P.bf, disparity);
+                        uRight = bestuR;
+                        sadOut = best;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) { P.uRight[iL] = uRight; P.depth[iL] = depth; P.sad[iL] = sadOut; }
+}
+
+__global__ void __launch_bounds__(1024) k_stereo_median(const __grid_constant__ StereoParams P, int *nValid)
+{
+    __shared__ int s_median, s_cnt, s_removed;
+    const int nL = *P.L.n;
+    if (threadIdx.x == 0) { s_median = -1; s_cnt = 0; s_removed = 0; }
+    __syncthreads();
+    int c = 0;
+    for (int i = threadIdx.x; i < nL; i += blockDim.x) c += P.sad[i] >= 0;
+    if (c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    const int n = s_cnt, k = n / 2;
+    if (n == 0) { if (threadIdx.x == 0) *nValid = 0; return; }
+    // the k-th smallest value v: #(< v) <= k < #(<= v)
+    for (int i = threadIdx.x; i < nL; i += blockDim.x) {
+        const int v = P.sad[i];
+        if (v < 0) continue;
+        int lt = 0, le = 0;
+        for (int j = 0; j < nL; j++) {
+            const int u = P.sad[j];
+            if (u >= 0) { lt += u < v; le += u <= v; }
+        }
+        if (lt <= k && k < le) s_median = v;
+    }
+    __syncthreads();
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);
+    int removed = 0;
+    for (int i = threadIdx.x; i < nL; i += blockDim.x) {
+        const int v = P.sad[i];
+        if (v >= 0 && !((float)v < thDist)) { P.uRight[i] = -1.f; P.depth[i] = -1.f; removed++; }
+    }
+    if (removed) atomicAdd(&s_removed, removed);
+    __syncthreads();
+    if (threadIdx.x == 0) *nValid = n - s_removed;
+}
+
+int stereo_match_impl(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight, float *depth,
+                      int *n_valid);
+
+} // namespace orbb200

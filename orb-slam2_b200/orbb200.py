@@ -23,7 +23,7 @@ EXPORTS = [
     "orbb200_extractor_stage_ms", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
     "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_merge_top2",
-    "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_last_error", "orbb200_version",
+    "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
 ]
 
 _lib = None
@@ -68,8 +68,15 @@ def lib():
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
+    L.orbb200_popc_peak.argtypes = [ip, C.POINTER(C.c_double)]
     _lib = L
     return L
+
+
+def popc_peak(device=-1):
+    v = C.c_double()
+    check(lib().orbb200_popc_peak(device, C.byref(v)))
+    return v.value
 
 
 def check(rc):

@@ -1,0 +1,123 @@
+"""GPU parity tests (through the C-ABI) of the extraction path against the CPU oracle.
+Tolerances (BASELINE.json north_star): keypoint x, y, octave, size, response and ORDER bit-exact; angle
+within 1e-4 rad; descriptors bit-exact for >= 99.9 % of keypoints."""
+import numpy as np
+import pytest
+
+import orbb200
+import ref_cpu
+import synth
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = float(np.degrees(1e-4))
+
+
+def _compare(kg, dg, kc, dc):
+    assert len(kg) == len(kc), (len(kg), len(kc))
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(kg[f], kc[f]), (f, np.flatnonzero(kg[f] != kc[f])[:8])
+    da = np.abs(kg["angle"].astype(np.float64) - kc["angle"].astype(np.float64))
+    da = np.minimum(da, 360.0 - da)
+    assert da.max() <= ANGLE_TOL_DEG, da.max()
+    bad = (dg != dc).any(axis=1).sum()
+    assert bad <= 0.001 * len(kc), "descriptor mismatch on %d of %d keypoints" % (bad, len(kc))
+    return int((kg["angle"] != kc["angle"]).sum()), int(bad)
+
+
+@pytest.mark.parametrize("name", ["tum", "kitti", "euroc"])
+def test_stages_and_outputs_match_oracle(configs, name):
+    w, h, nf, sfac, nl, ini, mn = configs[name]
+    img = synth.textured_frame(w, h, 1000)
+    ref = ref_cpu.RefExtractor(nf, sfac, nl, ini, mn)
+    kc, dc = ref.extract(img)
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    tb = ref.tables()
+    assert np.array_equal(ex.GetScaleFactors(), tb["scale"]) and np.array_equal(ex.GetInverseScaleFactors(), tb["inv_scale"])
+    assert np.array_equal(ex.GetScaleSigmaSquares(), tb["sigma2"])
+    assert np.array_equal(ex.GetInverseScaleSigmaSquares(), tb["inv_sigma2"])
+    assert np.array_equal(ex.GetFeaturesPerLevel(), tb["nfeat"])
+    kg, dg = ex(img)
+    for l in range(nl):
+        assert np.array_equal(ex.pyramid_level(l), ref.level_image(l)), ("pyramid", l)
+        c = ref.level_candidates(l)
+        g = ex.debug_candidates(l)
+        assert len(g) == len(c), ("ncand", l, len(g), len(c))
+        assert np.array_equal(g[:, 0], c["x"]) and np.array_equal(g[:, 1], c["y"]) and np.array_equal(g[:, 2], c["resp"]), ("cand", l)
+        rb = ref.level_blurred(l)
+        if rb is not None:
+            assert np.array_equal(ex.debug_blurred_level(l), rb), ("blur", l)
+    nang, nbad = _compare(kg, dg, kc, dc)
+    print(name, "kps", len(kg), "angle bit-diffs", nang, "descriptor row diffs", nbad)
+
+
+def test_golden_fixture_kitti(configs):
+    import os
+    path = os.path.join(os.path.dirname(__file__), "golden", "extract_kitti.npz")
+    g = np.load(path)
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    img = synth.textured_frame(w, h, int(g["seed"]))
+    kg, dg = orbb200.ORBextractor(nf, sfac, nl, ini, mn)(img)
+    _compare(kg, dg, g["kps"], g["desc"])
+
+
+def test_batch_equals_single_and_is_deterministic(configs):
+    w, h, nf, sfac, nl, ini, mn = configs["euroc"]
+    imgs = np.stack([synth.textured_frame(w, h, 2000 + k) for k in range(5)])
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kps, desc, n = ex.extract_batch(imgs)
+    kps2, desc2, n2 = ex.extract_batch(imgs)
+    assert np.array_equal(n, n2)
+    for b in range(5):
+        ks, ds = orbb200.ORBextractor(nf, sfac, nl, ini, mn)(imgs[b])
+        assert n[b] == len(ks)
+        assert np.array_equal(kps[b, :n[b]], ks) and np.array_equal(desc[b, :n[b]], ds)
+        assert np.array_equal(kps2[b, :n[b]], ks) and np.array_equal(desc2[b, :n[b]], ds)
+    ref = ref_cpu.RefExtractor(nf, sfac, nl, ini, mn)
+    for b in (0, 4):
+        kc, dc = ref.extract(imgs[b])
+        _compare(kps[b, :n[b]], desc[b, :n[b]], kc, dc)
+
+
+@pytest.mark.parametrize("shape,params", [
+    ((200, 150), (300, 1.2, 6, 20, 7)),      # small image, few cells
+    ((333, 517), (500, 1.3, 5, 15, 5)),      # portrait, other scale factor and thresholds
+    ((1000, 90), (400, 1.2, 4, 12, 7)),      # panorama: many quadtree roots
+    ((641, 479), (5000, 1.2, 8, 20, 7)),     # quota above the candidate count (quadtree runs dry)
+    ((640, 480), (40, 1.2, 8, 20, 7)),       # tiny quota (N < initial nodes)
+])
+def test_edge_shapes(shape, params):
+    w, h = shape
+    img = synth.textured_frame(w, h, 77)
+    ref = ref_cpu.RefExtractor(*params)
+    kc, dc = ref.extract(img)
+    ex = orbb200.ORBextractor(*params)
+    kg, dg = ex(img)
+    for l in range(params[2]):
+        assert np.array_equal(ex.pyramid_level(l), ref.level_image(l)), ("pyramid", l)
+    _compare(kg, dg, kc, dc)
+
+
+def test_flat_and_empty_images():
+    ex = orbb200.ORBextractor(1000, 1.2, 8, 20, 7)
+    k, d = ex(np.full((480, 640), 128, np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    k, d = ex(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0
+    # unaligned row stride (ROI of a larger image), as cv::Mat ROIs are
+    big = synth.textured_frame(700, 500, 5)
+    roi = big[7:487, 13:653]
+    kc, dc = ref_cpu.RefExtractor(1000, 1.2, 8, 20, 7).extract(np.ascontiguousarray(roi))
+    kg, dg = ex(roi)
+    _compare(kg, dg, kc, dc)
+
+
+def test_large_image_4k_properties():
+    """BASELINE config 4 (3840x2160, 8000 feats, 12 levels): parity vs the oracle on the full size."""
+    img = synth.textured_frame(3840, 2160, 4000)
+    params = (8000, 1.2, 12, 20, 7)
+    ex = orbb200.ORBextractor(*params)
+    kg, dg = ex(img)
+    kc, dc = ref_cpu.RefExtractor(*params).extract(img)
+    _compare(kg, dg, kc, dc)
+    assert len(kg) >= 8000

@@ -1,0 +1,107 @@
+"""GPU parity tests (through the C-ABI) of the matcher kernels against the CPU oracle: match indices bit-exact."""
+import numpy as np
+import pytest
+
+import orbb200
+import ref_cpu
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _eq(a, b, fields=("best_dist", "best_idx", "second_dist", "second_idx")):
+    for f in fields:
+        assert np.array_equal(a[f], b[f]), (f, np.flatnonzero(a[f] != b[f])[:8])
+
+
+def test_descriptor_distance():
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (5000, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (5000, 32), dtype=np.uint8)
+    b[10] = a[10]
+    b[11] = ~a[11]
+    d = orbb200.ORBmatcher().DescriptorDistance(a, b)
+    ref = np.unpackbits(a ^ b, axis=1).sum(axis=1)
+    assert np.array_equal(d, ref) and d[10] == 0 and d[11] == 256
+    assert ref_cpu.descriptor_distance(a[0], b[0]) == d[0]
+
+
+@pytest.mark.parametrize("nq,ndb", [(1, 1), (3, 5), (37, 127), (64, 128), (513, 1000), (2048, 20000)])
+def test_bruteforce_top2_equals_oracle(nq, ndb):
+    q, db, _ = synth.descriptor_db(nq, ndb, seed=nq + ndb)
+    # duplicates and ties: copies of rows at several positions
+    if ndb > 40:
+        db[ndb - 1] = db[7]
+        db[20] = db[7]
+        q[0] = db[7]
+    t = orbb200.ORBmatcher().bruteforce_top2(q, db)
+    _eq(t, ref_cpu.bf_top2(q, db))
+
+
+def test_bruteforce_all_equal_rows_first_index_wins():
+    db = np.zeros((3000, 32), np.uint8)
+    q = np.zeros((10, 32), np.uint8)
+    t = orbb200.ORBmatcher().bruteforce_top2(q, db)
+    assert (t["best_idx"] == 0).all() and (t["second_idx"] == 1).all() and (t["best_dist"] == 0).all()
+    _eq(t, ref_cpu.bf_top2(q, db))
+
+
+def test_sharded_merge_equals_flat():
+    """config 5 structure: database split by rows, per-shard top-2 with global indices, then merge."""
+    nq, ndb, shards = 256, 8192, 8
+    q, db, _ = synth.descriptor_db(nq, ndb, seed=5)
+    db[5000] = db[100]
+    q[3] = db[100]
+    m = orbb200.ORBmatcher()
+    parts = np.zeros((shards, nq), orbb200.TOP2_DTYPE)
+    per = ndb // shards
+    for s in range(shards):
+        p = m.bruteforce_top2(q, db[s * per:(s + 1) * per])
+        for f in ("best_idx", "second_idx"):
+            p[f] = np.where(p[f] >= 0, p[f] + s * per, -1)
+        parts[s] = p
+    merged = m.merge_top2(parts)
+    _eq(merged, ref_cpu.bf_top2(q, db))
+    acc = m.accept_ratio(merged)
+    r = ref_cpu.bf_top2(q, db)
+    ref_acc = np.array([ref_cpu.lib().ref_ratio_accept(int(a), int(b), 50, float(np.float32(0.6))) for a, b in
+                        zip(r["best_dist"], r["second_dist"])], bool)
+    assert np.array_equal(acc, ref_acc) and acc.any() and not acc.all()
+
+
+def test_match_candidates_equals_oracle():
+    rng = np.random.default_rng(9)
+    nq, nt = 1500, 1800
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    t[5] = t[900]
+    counts = rng.integers(0, 90, nq)
+    counts[0] = 0
+    counts[1] = 1
+    counts[2] = 400
+    offs = np.zeros(nq + 1, np.int32)
+    offs[1:] = np.cumsum(counts)
+    idx = rng.integers(0, nt, offs[-1]).astype(np.int32)
+    idx[offs[2]:offs[2] + 3] = [900, 5, 900]  # equal distances: first in list order wins
+    g = orbb200.ORBmatcher().match_candidates(q, t, offs, idx)
+    _eq(g, ref_cpu.match_candidates(q, t, offs, idx))
+    assert g["best_idx"][0] == -1 and g["best_dist"][0] == 256
+
+
+def test_stereo_match_equals_oracle(configs):
+    """BASELINE config 2: KITTI-shape stereo pair, extraction of both images + ComputeStereoMatches."""
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    left, right = synth.stereo_pair(w, h, 1001)
+    exL, exR = orbb200.ORBextractor(nf, sfac, nl, ini, mn), orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kL, dL = exL(left)
+    kR, dR = exR(right)
+    bf, fx = 386.1448, 718.856
+    b = bf / fx
+    uR, depth, nvalid = orbb200.stereo_match(exL, exR, bf, b)
+    pyrL = [exL.pyramid_level(l) for l in range(nl)]
+    pyrR = [exR.pyramid_level(l) for l in range(nl)]
+    ruR, rdepth, _, rn = ref_cpu.stereo_match(kL, dL, kR, dR, pyrL, pyrR, exL.GetScaleFactors(), exL.GetInverseScaleFactors(), bf, b)
+    n = len(kL)
+    assert rn > 200, rn
+    assert nvalid == rn
+    assert np.array_equal(uR[:n], ruR) and np.array_equal(depth[:n], rdepth)
