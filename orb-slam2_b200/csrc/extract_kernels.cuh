@@ -301,14 +301,18 @@ __device__ __forceinline__ int fast_arc_strength(const uint8_t *c, int th)
         mn3[k] = __vimin3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
         mx3[k] = __vimax3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
     }
-    int best = 0;
+    // NOTE: keep the two reductions separate and negate once at the end.  ptxas 12.9 (sm_100a) miscompiles
+    // max(best, mn9, -mx9) -- it folds the negation into VIMNMX3 and drops it (verified on a B200 with
+    // tools/scratch/vimnmx.cu: even the plain-loop form returns max(d) instead of the arc strength).
+    int bmn = 0, bmx = 0x7fffffff;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
         const int mn9 = __vimin3_s32(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
         const int mx9 = __vimax3_s32(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-        best = __vimax3_s32(best, mn9, -mx9);
+        bmn = max(bmn, mn9);
+        bmx = min(bmx, mx9);
     }
-    return best;
+    return max(bmn, -bmx);
 }
 
 __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant__ ExtractParams P)
