@@ -1,0 +1,461 @@
+#!/usr/bin/env python
+"""bench.py -- ORB front-end hot path on B200: KITTI-shape stereo extraction (+ ComputeStereoMatches) frames/s,
+and brute-force Hamming top-2 match pairs/s, with HBM / POPC rooflines and the CPU port timed beside them.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--pairs P] [--impl b200|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+         bench.py --gpus N --steps K --warmup W
+
+One step = one pass of the hot path over one batch of P synthetic KITTI-shape stereo pairs per GPU (2P images of
+1241x376, 2000 features, 8 levels, FAST 20/7): pyramid -> FAST cells -> quadtree -> blur -> orientation +
+descriptors for all 2P images, then Frame::ComputeStereoMatches for the P pairs.  Frames are sharded over the ranks
+(weak scaling, no data-path collective).  `value` = images/s with inputs resident in HBM; `e2e` = images/s through
+the host-buffer C-ABI (orbb200_extract_batch + orbb200_stereo_match_batch) with pinned host inputs/outputs and
+all H2D/D2H copies inside the timed region.  The `match` object is BASELINE config 5 (2 048 queries x 1 048 576
+database rows, database row-sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge kernel).
+
+PyTorch is plumbing only here (device buffers, pinned memory, torch.distributed); every kernel launched inside
+the timed regions is one of liborbb200.so's.  oracle/ (the CPU port) is executed only for `cpu_baseline` and for
+`--impl reference`.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "orb-slam2_b200"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+KITTI = dict(w=1241, h=376, nfeatures=2000, scale=1.2, nlevels=8, ini=20, min=7, bf=386.1448, fx=718.856)
+METRIC = "ORB extract frames/s @KITTI 1241x376 2k feats"
+WORKLOAD = "kitti_stereo_1241x376_L+R_2000feat_8lvl_extract+ComputeStereoMatches"
+NQ, NDB = 2048, 1 << 20
+
+
+def level_sizes(w, h, scale, nlevels):
+    """pyramid level shapes exactly as ORBextractor.cc:450,459,1351-1353 (f32 running product, cvRound)."""
+    sf = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        sf.append(np.float32(np.float64(sf[-1]) * np.float64(np.float32(scale))))
+    out = []
+    for s in sf:
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes(w, h, scale, nlevels, nkp):
+    """per-stage algorithmic bytes of one extracted image."""
+    P = [a * b for a, b in level_sizes(w, h, scale, nlevels)]
+    tot = sum(P)
+    stages = {
+        "pyramid": sum(P[l - 1] + P[l] for l in range(1, nlevels)),
+        "fast_cells": tot,
+        "octree_select": 0,
+        "blur7": 2 * tot,
+        "orient_describe": nkp * (749 + 512 + 32 + 28),
+    }
+    return stages, sum(stages.values())
+
+
+def make_pairs(npairs, seed0=1000, nbase=6):
+    """npairs stereo pairs [2*npairs, H, W] u8, interleaved L,R.  A few seeded base pairs (synth.stereo_pair) are
+    expanded by row-rolls, which keep the per-row disparity structure and give distinct pixel data per pair."""
+    import synth
+    w, h = KITTI["w"], KITTI["h"]
+    base = [synth.stereo_pair(w, h, seed0 + k) for k in range(min(nbase, npairs))]
+    out = np.empty((2 * npairs, h, w), np.uint8)
+    for p in range(npairs):
+        L, R = base[p % len(base)]
+        sh = (p // len(base)) * 13
+        out[2 * p] = np.roll(L, sh, axis=0)
+        out[2 * p + 1] = np.roll(R, sh, axis=0)
+    return out
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU through NVML while the timed region runs"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# --------------------------------------------------------------------------------------------- CPU port arm
+def cpu_extract_pairs(imgs, nthreads):
+    """the oracle port (oracle/orb_ref.c) on host threads: extraction of every image + ComputeStereoMatches per
+    pair; returns (seconds, images).  ctypes releases the GIL inside the C calls."""
+    import ref_cpu
+    from concurrent.futures import ThreadPoolExecutor
+    K = KITTI
+    npairs = len(imgs) // 2
+    b = K["bf"] / K["fx"]
+    tl = threading.local()
+
+    def work(p):
+        if not hasattr(tl, "ex"):
+            tl.ex = (ref_cpu.RefExtractor(K["nfeatures"], K["scale"], K["nlevels"], K["ini"], K["min"]),
+                     ref_cpu.RefExtractor(K["nfeatures"], K["scale"], K["nlevels"], K["ini"], K["min"]))
+        eL, eR = tl.ex
+        kL, dL = eL.extract(imgs[2 * p])
+        kR, dR = eR.extract(imgs[2 * p + 1])
+        pyrL = [eL.level_image(l) for l in range(K["nlevels"])]
+        pyrR = [eR.level_image(l) for l in range(K["nlevels"])]
+        tb = eL.tables()
+        ref_cpu.stereo_match(kL, dL, kR, dR, pyrL, pyrR, tb["scale"], tb["inv_scale"], K["bf"], b)
+        return len(kL)
+
+    with ThreadPoolExecutor(nthreads) as ex:
+        list(ex.map(work, range(min(nthreads, npairs))))  # warm: build per-thread extractors
+        t0 = time.perf_counter()
+        list(ex.map(work, range(npairs)))
+        dt = time.perf_counter() - t0
+    return dt, 2 * npairs
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU implementation of the path on the box's host cores.  OpenCV C++ is not on this
+    image, so the untouched reference cannot be compiled; the timed code is the plain-C port."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    npairs = max(cores, 8)
+    imgs = make_pairs(npairs)
+    for _ in range(args.warmup):
+        cpu_extract_pairs(imgs[:2 * min(npairs, cores)], cores)
+    tot_t, tot_img = 0.0, 0
+    for _ in range(args.steps):
+        dt, n = cpu_extract_pairs(imgs, cores)
+        tot_t += dt
+        tot_img += n
+    v = tot_img / tot_t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "pairs_per_step": npairs, "images_per_step": 2 * npairs},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
+                         "sample": "%d stereo pairs per step x %d steps, one extractor pair per thread" % (npairs, args.steps)},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- B200 arm
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import orbb200
+    import synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    K = KITTI
+    P = args.pairs
+    B = 2 * P
+    w, h = K["w"], K["h"]
+    bconst = K["bf"] / K["fx"]
+    ex = orbb200.ORBextractor(K["nfeatures"], K["scale"], K["nlevels"], K["ini"], K["min"], device=local_rank)
+    cap = ex.cap
+    stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+
+    # ---- inputs: pinned host copy (e2e) and device-resident copy (value); different pairs on every rank
+    host_imgs = torch.empty((B, h, w), dtype=torch.uint8).pin_memory()
+    host_imgs.numpy()[:] = make_pairs(P, seed0=1000 + 97 * rank)
+    dev_imgs = host_imgs.to(dev)
+    kps_d = torch.empty((B, cap, 7), dtype=torch.float32, device=dev)
+    desc_d = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    n_d = torch.zeros((B,), dtype=torch.int32, device=dev)
+    uR_d = torch.empty((P, cap), dtype=torch.float32, device=dev)
+    dep_d = torch.empty((P, cap), dtype=torch.float32, device=dev)
+    nv_d = torch.zeros((P,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def step_device():
+        ex.extract_batch_device(dev_imgs.data_ptr(), B, w, h, w, w * h, kps_d.data_ptr(), desc_d.data_ptr(), cap, n_d.data_ptr())
+        ex.stereo_match_batch_device(P, K["bf"], bconst, uR_d.data_ptr(), dep_d.data_ptr(), nv_d.data_ptr())
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    ex.sync()
+    launches_per_step = ex.last_launches() + 2
+    ex.set_profiling(True)  # stage events on the handle's stream, inside the timed region
+    sampler = ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.start()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    ex.sync()
+    barrier()
+    sampler.stop_flag = True
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    stage_sum, ncalls = ex.stage_ms_sum()
+    ex.set_profiling(False)
+    ms_per_step = ms_total / args.steps
+    value = world * B * args.steps / (ms_total * 1e-3)
+    n_host = n_d.cpu().numpy()
+    nv_host = nv_d.cpu().numpy()
+    mean_kp = float(n_host.mean())
+
+    # ---- roofline of the dominant kernel (per-stage CUDA-event time inside the timed region)
+    stage_ms = {k: v / max(ncalls, 1) for k, v in stage_sum.items()}
+    stage_ms["stereo_match"] = max(ms_per_step - sum(stage_ms.values()), 0.0) if ncalls == args.steps else None
+    abytes, abytes_img = algorithmic_bytes(w, h, K["scale"], K["nlevels"], mean_kp)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    dom = max((k for k in ex.STAGES), key=lambda k: stage_ms[k])
+    dom_launches = (K["nlevels"] - 1) if dom == "pyramid" else 1
+    dom_bytes = abytes[dom] * B  # algorithmic bytes all launches of that stage move in one step
+    dom_bytes_note = None
+    if dom == "octree_select":  # no image traffic: candidates in (4 B) + selected out (4 B)
+        dom_bytes = 0
+        dom_bytes_note = "quadtree selection moves no image bytes; it is latency/serial bound (see DESIGN.md)"
+    achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+    roofline = {
+        "kernel": "k_" + dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+        "launches_per_step": dom_launches, "ms_per_step": stage_ms[dom], "algorithmic_bytes_per_step": dom_bytes,
+        "stage_ms_per_step": stage_ms,
+        "path": {"algorithmic_bytes_per_image": abytes_img, "achieved": value / world * abytes_img / 1e9,
+                 "frac": value / world * abytes_img / 1e9 / hbm_peak, "unit": "GB/s"},
+    }
+    if dom_bytes_note:
+        roofline["note"] = dom_bytes_note
+
+    # ---- e2e: host buffers through the C-ABI, copies inside the timed region
+    kps_h = torch.empty((B, cap, 7), dtype=torch.float32).pin_memory()
+    desc_h = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    n_h = torch.zeros((B,), dtype=torch.int32).pin_memory()
+    uR_h = torch.empty((P, cap), dtype=torch.float32).pin_memory()
+    dep_h = torch.empty((P, cap), dtype=torch.float32).pin_memory()
+    nv_h = torch.zeros((P,), dtype=torch.int32).pin_memory()
+    import ctypes as C
+    ptrs = (C.c_void_p * B)(*[host_imgs.data_ptr() + b * w * h for b in range(B)])
+    L = orbb200.lib()
+
+    def step_host():
+        orbb200.check(L.orbb200_extract_batch(ex.h, ptrs, B, w, h, w, kps_h.data_ptr(), desc_h.data_ptr(), cap, n_h.data_ptr()))
+        orbb200.check(L.orbb200_stereo_match_batch(ex.h, P, K["bf"], bconst, uR_h.data_ptr(), dep_h.data_ptr(), nv_h.data_ptr()))
+
+    for _ in range(2):
+        step_host()
+    e2e_steps = max(1, min(args.steps, 10))
+    barrier()
+    e0.record(stream)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()
+    e1.record(stream)
+    ex.sync()
+    wall = time.perf_counter() - t0
+    barrier()
+    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), wall * 1e3))
+    e2e_value = world * B * e2e_steps / (e2e_ms * 1e-3)
+    h2d = B * w * h
+    d2h = B * cap * (28 + 32) + B * 4 + 2 * P * cap * 4 + P * 4
+    assert np.array_equal(n_h.numpy(), n_host), "host-API and device-API keypoint counts differ"
+
+    # ---- config 5: brute-force top-2, database sharded by rows over the ranks
+    match = bench_match(args, rank, world, dev, barrier, max_over_ranks)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "pairs_per_step_per_gpu": P, "images_per_step_per_gpu": B,
+                   "input_bytes_per_step_per_gpu": B * w * h, "l2_policy": "inputs larger than L2 (126 MB)" if B * w * h > 126e6 else
+                   "inputs smaller than L2: raise --pairs", "mean_keypoints_per_image": mean_kp,
+                   "mean_stereo_matches_per_pair": float(nv_host.mean()), "sharding": "frames per GPU, no collective"},
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps, "api": "orbb200_extract_batch + orbb200_stereo_match_batch (pinned host buffers)"},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": roofline,
+        "clocks": sampler.summary(),
+        "match": match,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        sample_pairs = max(cores, 8) * 2
+        dt, nimg = cpu_extract_pairs(host_imgs.numpy()[:2 * sample_pairs], cores)
+        line["cpu_baseline"] = {"value": nimg / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+                                "sample": "%d of the step's stereo pairs (extraction L+R + ComputeStereoMatches), oracle/orb_ref.c, "
+                                          "one extractor pair per thread, %.1f s wall" % (sample_pairs, dt)}
+        line["match"]["cpu_baseline"] = cpu_match_baseline(cores)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def bench_match(args, rank, world, dev, barrier, max_over_ranks):
+    import torch
+    import torch.distributed as dist
+    import orbb200
+    import synth
+    L = orbb200.lib()
+    q, db, _ = synth.descriptor_db(NQ, NDB, seed=7)
+    per = NDB // world
+    lo = rank * per
+    q_d = torch.from_numpy(q).to(dev)
+    db_d = torch.from_numpy(np.ascontiguousarray(db[lo:lo + per])).to(dev)
+    part_d = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
+    gath_d = torch.empty((world, NQ, 4), dtype=torch.int32, device=dev)
+    out_d = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
+    ts = torch.cuda.Stream(device=dev)  # a real (non-default) stream: kernels, NCCL and events all order on it
+    torch.cuda.set_stream(ts)
+    st = ts.cuda_stream
+
+    def step():
+        orbb200.check(L.orbb200_match_bruteforce_top2_device(q_d.data_ptr(), NQ, db_d.data_ptr(), per, part_d.data_ptr(), lo, st))
+        if world > 1:
+            dist.all_gather_into_tensor(gath_d, part_d)
+            orbb200.check(L.orbb200_merge_top2_device(gath_d.data_ptr(), world, NQ, out_d.data_ptr(), st))
+
+    for _ in range(3):
+        step()
+    steps = max(args.steps, 5)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+    pairs = float(NQ) * NDB
+    popc = orbb200.popc_peak(dev.index)
+    val = pairs / (ms * 1e-3)
+    res = out_d if world > 1 else part_d
+    r = res.cpu().numpy()
+    m = {
+        "metric": "Hamming match pairs/s (brute-force top-2, 2048 queries x 1048576 rows)", "value": val, "unit": "pairs/s",
+        "ms_per_step": ms, "scaling": "strong", "sharding": "database rows / rank, NCCL all-gather of per-shard top-2 + merge"
+        if world > 1 else "single GPU",
+        "gpu_launches_per_step": 2 + (1 if world > 1 else 0),
+        "roofline": {"kernel": "k_bf_top2", "bound": "popc", "achieved": val * 8 / world / 1e12, "peak": popc / 1e12,
+                     "unit": "Tpopc32/s", "frac": val * 8 / world / popc,
+                     "peak_source": "orbb200_popc_peak microbenchmark run in this process"},
+        "checksum": int(r[:, 1].astype(np.int64).sum()),
+    }
+    return m
+
+
+def cpu_match_baseline(cores):
+    """the bit-hack DescriptorDistance loop of ORBmatcher.cc:1733-1749 (oracle port) on all host cores"""
+    import ref_cpu
+    import synth
+    from concurrent.futures import ThreadPoolExecutor
+    nq, ndb = 256, 1 << 16
+    q, db, _ = synth.descriptor_db(nq, ndb, seed=7)
+    chunks = np.array_split(np.arange(nq), cores)
+
+    def work(ix):
+        if len(ix):
+            ref_cpu.bf_top2(q[ix], db)
+
+    with ThreadPoolExecutor(cores) as ex:
+        list(ex.map(work, chunks))
+        t0 = time.perf_counter()
+        reps = 4
+        for _ in range(reps):
+            list(ex.map(work, chunks))
+        dt = time.perf_counter() - t0
+    return {"value": reps * nq * ndb / dt, "unit": "pairs/s", "cores": cores, "kind": "port",
+            "sample": "%d queries x %d rows x %d reps, queries split over threads" % (nq, ndb, reps)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=160, help="stereo pairs per step per GPU (2x images)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # plain `python bench.py --gpus N`: re-launch under torchrun, one rank per GPU
+        import subprocess
+        port = 29500 + os.getpid() % 2000
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -91,6 +91,9 @@ int orbb200_extractor_sync(orbb200_extractor *e);
  * stages: 0 pyramid, 1 fast_cells, 2 octree_select, 3 blur7, 4 orient_describe.  ms[5]. */
 int orbb200_extractor_set_profiling(orbb200_extractor *e, int on);
 int orbb200_extractor_stage_ms(orbb200_extractor *e, float *ms, int n);
+/* sum of the per-stage times over the calls recorded since profiling was switched on (at most the last 64);
+ * *ncalls = how many calls the sums cover.  Synchronises the handle's stream. */
+int orbb200_extractor_stage_ms_sum(orbb200_extractor *e, float *ms, int n, int *ncalls);
 /* number of kernel launches issued by the last extract call */
 int orbb200_extractor_last_launches(const orbb200_extractor *e);
 
@@ -134,6 +137,15 @@ int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, 
  * (-1 where unmatched).  bf = mbf, b = mb (baseline in metres). */
 int orbb200_stereo_match(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight,
                          float *depth, int *n_valid);
+
+/* F1 for a batch of stereo pairs held by ONE handle: the last orbb200_extract_batch[_device] call on `e` carried
+ * the pairs interleaved (image 2p = left, 2p+1 = right view of pair p).  Outputs are [npairs][cap] with cap the
+ * capacity of that extract call; entries past a pair's left keypoint count are unspecified.  The _device variant
+ * is asynchronous on the handle's stream. */
+int orbb200_stereo_match_batch(orbb200_extractor *e, int npairs, float bf, float b, float *uRight, float *depth,
+                               int *n_valid);
+int orbb200_stereo_match_batch_device(orbb200_extractor *e, int npairs, float bf, float b, float *uRight_d,
+                                      float *depth_d, int *n_valid_d);
 
 /* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
  * roofline; runs a dependent-free popc microkernel for a few milliseconds. */

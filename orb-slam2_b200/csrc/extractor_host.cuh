@@ -33,6 +33,11 @@ struct orbb200_extractor {
     uint8_t *d_desc = nullptr;
     int *d_nOut = nullptr;
     int outCap = 0, outBatch = 0;
+    // batched stereo matcher scratch / outputs (orbb200_stereo_match_batch*)
+    float *d_stU = nullptr, *d_stD = nullptr;
+    int *d_stSad = nullptr, *d_stN = nullptr;
+    size_t stElems = 0;
+    int stPairs = 0;
     // last call
     int lastBatch = 0, lastCap = 0;
     const uint8_t *lastL0 = nullptr;
@@ -44,8 +49,9 @@ struct orbb200_extractor {
     int lastLaunches = 0;
     // profiling
     int profiling = 0;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    bool evValid = false;
+    static constexpr int EV_RING = 64;
+    cudaEvent_t ev[EV_RING][6] = {}; // ring of per-call stage event sets, created when profiling is switched on
+    int evCount = 0;                 // calls recorded since profiling was enabled
 };
 
 namespace orbb200 {

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree_select(const __grid_cons
                 const int ex = block_excl_scan(f, scanTmp, &tot);
                 if (p < size) vrank[p] = -1;
                 if (f)
-                    skeys[nvis + ex] = ((unsigned long long)cur.cnt[p] << 43) | ((unsigned long long)cur.seq[p] << 20) |
+                    skeys[nvis + ex] = ((unsigned long long)cur.cnt[p] << 40) | ((unsigned long long)(cur.seq[p] & 0xFFFFF) << 20) |
                                        (unsigned long long)p;
                 nvis += tot;
             }
@@ -290,10 +290,10 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree_select(const __grid_cons
     for (int p = tid; p < size; p += NT) best[p] = 0u;
     __syncthreads();
     for (int i = tid; i < n; i += NT)
-        atomicMax(&best[knode[i]], ((ord[i] >> 24) << 21) | (0x1FFFFFu - (unsigned int)i));
+        atomicMax(&best[knode[i]], ((ord[i] >> 24) << 24) | (0xFFFFFFu - (unsigned int)i));
     __syncthreads();
     uint32_t *out = P.lvlKp + (size_t)b * P.nodeTotal + g.nodeOff;
-    for (int p = tid; p < size; p += NT) out[p] = ord[0x1FFFFFu - (best[p] & 0x1FFFFFu)];
+    for (int p = tid; p < size; p += NT) out[p] = ord[0xFFFFFFu - (best[p] & 0xFFFFFFu)];
     if (tid == 0) P.lvlCount[(size_t)b * P.nlevels + l] = size;
 }
 

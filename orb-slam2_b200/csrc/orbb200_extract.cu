@@ -67,7 +67,7 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
             g.cellCap = ((g.wCell + 1) / 2) * ((g.hCell + 1) / 2);
             g.candOff = (unsigned int)candOff;
             g.candCap = g.nCells * g.cellCap;
-            if (g.candCap > (1 << 21) - 1) { set_error("level %d: candidate capacity %d exceeds 2^21", l, g.candCap); return ORBB200_ERR_ARG; }
+            if (g.candCap > (1 << 24) - 1) { set_error("level %d: candidate capacity %d exceeds 2^24", l, g.candCap); return ORBB200_ERR_ARG; }
             candOff += align_up((size_t)g.candCap, 64);
             g.nfeat = e->nfeat[l];
             int nIni = 1;

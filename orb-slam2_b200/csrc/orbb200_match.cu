@@ -220,4 +220,15 @@ int orbb200_stereo_match(orbb200_extractor *left, orbb200_extractor *right, floa
     return stereo_match_impl(left, right, bf, b, uRight, depth, n_valid);
 }
 
+int orbb200_stereo_match_batch_device(orbb200_extractor *e, int npairs, float bf, float b, float *uRight_d, float *depth_d,
+                                      int *n_valid_d)
+{
+    return stereo_batch_device_impl(e, npairs, bf, b, uRight_d, depth_d, n_valid_d);
+}
+
+int orbb200_stereo_match_batch(orbb200_extractor *e, int npairs, float bf, float b, float *uRight, float *depth, int *n_valid)
+{
+    return stereo_batch_host_impl(e, npairs, bf, b, uRight, depth, n_valid);
+}
+
 } // extern "C"

@@ -18,7 +18,20 @@ struct StereoSide {
     const uint8_t *l0;
     int l0Pitch;
     const uint8_t *pyr;
+    // batch strides from pair p to pair p+1 (0 for the single-pair call)
+    size_t kpStride, nStride, l0Stride, pyrStride;
 };
+
+__device__ __forceinline__ StereoSide stereo_side(const StereoSide &s, int pair)
+{
+    StereoSide r = s;
+    r.kps += pair * s.kpStride;
+    r.desc += pair * s.kpStride * 32;
+    r.n += pair * s.nStride;
+    r.l0 += pair * s.l0Stride;
+    r.pyr += pair * s.pyrStride;
+    return r;
+}
 
 struct StereoParams {
     StereoSide L, R;
@@ -28,6 +41,8 @@ struct StereoParams {
     float sf[ORBB200_MAX_LEVELS], isf[ORBB200_MAX_LEVELS];
     float *uRight, *depth;
     int *sad; // SAD distance per left keypoint, -1 when no depth
+    size_t outStride; // per-pair stride of uRight / depth / sad
+    int cap;          // keypoint capacity per image (counts are clamped to it)
 };
 
 __device__ __forceinline__ const uint8_t *stereo_level(const StereoSide &s, const LevelGeom &g, int l, int &pitch)
@@ -41,9 +56,11 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
 {
     const int lane = threadIdx.x & 31;
     const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nL = *P.L.n, nR = *P.R.n;
+    const int pair = blockIdx.y;
+    const StereoSide SL = stereo_side(P.L, pair), SR = stereo_side(P.R, pair);
+    const int nL = min(*SL.n, P.cap), nR = min(*SR.n, P.cap);
     if (iL >= nL) return;
-    const orbb200_keypoint kL = P.L.kps[iL];
+    const orbb200_keypoint kL = SL.kps[iL];
     float uRight = -1.f, depth = -1.f;
     int sadOut = -1;
     const int levelL = kL.octave;
@@ -55,15 +72,15 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
     top2_init(t);
     t.d1 = 100; // bestDist starts at TH_HIGH (:633)
     if (row >= 0 && row < P.nRows && !(maxU < 0)) {
-        const Desc dL = load_desc(P.L.desc + (size_t)iL * 32);
+        const Desc dL = load_desc(SL.desc + (size_t)iL * 32);
         for (int iR = lane; iR < nR; iR += 32) {
-            const orbb200_keypoint kR = P.R.kps[iR];
+            const orbb200_keypoint kR = SR.kps[iR];
             const float r = __fmul_rn(2.0f, P.sf[kR.octave]);
             const int maxr = (int)ceilf(__fadd_rn(kR.y, r)), minr = (int)floorf(__fsub_rn(kR.y, r));
             if (row < minr || row > maxr) continue;
             if (kR.octave < levelL - 1 || kR.octave > levelL + 1) continue;
             if (kR.x >= minU && kR.x <= maxU) {
-                const int d = hamming(dL, load_desc(P.R.desc + (size_t)iR * 32));
+                const int d = hamming(dL, load_desc(SR.desc + (size_t)iR * 32));
                 if (d < t.d1) { t.d1 = d; t.i1 = iR; }
             }
         }
@@ -75,7 +92,7 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
         if (lex_less(od, oi, t.d1, t.i1)) { t.d1 = od; t.i1 = oi; }
     }
     if (t.i1 >= 0 && t.d1 < 75) { // thOrbDist = (TH_HIGH+TH_LOW)/2 (:582,663)
-        const float uR0 = P.R.kps[t.i1].x;
+        const float uR0 = SR.kps[t.i1].x;
         const float scaleFactor = P.isf[levelL];
         const float scaleduL = roundf(__fmul_rn(uL, scaleFactor)), scaledvL = roundf(__fmul_rn(vL, scaleFactor));
         const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
@@ -87,7 +104,7 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
         const bool inImg = !(cy - 5 < 0 || cy + 5 >= H || cxl - 5 < 0 || cxl + 5 >= W || cxr - 10 < 0 || cxr + 10 >= W);
         if (inRef && inImg) {
             int pl, pr;
-            const uint8_t *IL = stereo_level(P.L, g, levelL, pl), *IR = stereo_level(P.R, g, levelL, pr);
+            const uint8_t *IL = stereo_level(SL, g, levelL, pl), *IR = stereo_level(SR, g, levelL, pr);
             const int lc = IL[(size_t)cy * pl + cxl];
             // each lane owns up to 4 of the 121 patch pixels; its left values are inc-independent
             int lv[4], off[4];
@@ -129,28 +146,35 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
             }
         }
     }
-    if (lane == 0) { P.uRight[iL] = uRight; P.depth[iL] = depth; P.sad[iL] = sadOut; }
+    if (lane == 0) {
+        const size_t o = (size_t)pair * P.outStride + iL;
+        P.uRight[o] = uRight; P.depth[o] = depth; P.sad[o] = sadOut;
+    }
 }
 
 __global__ void __launch_bounds__(1024) k_stereo_median(const __grid_constant__ StereoParams P, int *nValid)
 {
     __shared__ int s_median, s_cnt, s_removed;
-    const int nL = *P.L.n;
+    const int pair = blockIdx.x;
+    const int nL = min(P.L.n[pair * P.L.nStride], P.cap);
+    int *sad = P.sad + (size_t)pair * P.outStride;
+    float *uRight = P.uRight + (size_t)pair * P.outStride, *depth = P.depth + (size_t)pair * P.outStride;
+    nValid += pair;
     if (threadIdx.x == 0) { s_median = -1; s_cnt = 0; s_removed = 0; }
     __syncthreads();
     int c = 0;
-    for (int i = threadIdx.x; i < nL; i += blockDim.x) c += P.sad[i] >= 0;
+    for (int i = threadIdx.x; i < nL; i += blockDim.x) c += sad[i] >= 0;
     if (c) atomicAdd(&s_cnt, c);
     __syncthreads();
     const int n = s_cnt, k = n / 2;
     if (n == 0) { if (threadIdx.x == 0) *nValid = 0; return; }
     // the k-th smallest value v: #(< v) <= k < #(<= v)
     for (int i = threadIdx.x; i < nL; i += blockDim.x) {
-        const int v = P.sad[i];
+        const int v = sad[i];
         if (v < 0) continue;
         int lt = 0, le = 0;
         for (int j = 0; j < nL; j++) {
-            const int u = P.sad[j];
+            const int u = sad[j];
             if (u >= 0) { lt += u < v; le += u <= v; }
         }
         if (lt <= k && k < le) s_median = v;
@@ -159,8 +183,8 @@ __global__ void __launch_bounds__(1024) k_stereo_median(const __grid_constant__ 
     const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);
     int removed = 0;
     for (int i = threadIdx.x; i < nL; i += blockDim.x) {
-        const int v = P.sad[i];
-        if (v >= 0 && !((float)v < thDist)) { P.uRight[i] = -1.f; P.depth[i] = -1.f; removed++; }
+        const int v = sad[i];
+        if (v >= 0 && !((float)v < thDist)) { uRight[i] = -1.f; depth[i] = -1.f; removed++; }
     }
     if (removed) atomicAdd(&s_removed, removed);
     __syncthreads();
@@ -169,5 +193,8 @@ __global__ void __launch_bounds__(1024) k_stereo_median(const __grid_constant__ 
 
 int stereo_match_impl(orbb200_extractor *left, orbb200_extractor *right, float bf, float b, float *uRight, float *depth,
                       int *n_valid);
+int stereo_batch_device_impl(orbb200_extractor *e, int npairs, float bf, float b, float *uRight_d, float *depth_d,
+                             int *n_valid_d);
+int stereo_batch_host_impl(orbb200_extractor *e, int npairs, float bf, float b, float *uRight, float *depth, int *n_valid);
 
 } // namespace orbb200

@@ -20,10 +20,11 @@ EXPORTS = [
     "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_max_keypoints",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling",
-    "orbb200_extractor_stage_ms", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
+    "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
     "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_merge_top2",
-    "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
+    "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
+    "orbb200_stereo_match_batch_device", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
 ]
 
 _lib = None
@@ -58,6 +59,7 @@ def lib():
     L.orbb200_extractor_sync.argtypes = [vp]
     L.orbb200_extractor_set_profiling.argtypes = [vp, ip]
     L.orbb200_extractor_stage_ms.argtypes = [vp, vp, ip]
+    L.orbb200_extractor_stage_ms_sum.argtypes = [vp, vp, ip, vp]
     L.orbb200_extractor_last_launches.argtypes = [vp]
     L.orbb200_debug_candidates.argtypes = [vp, ip, ip, vp, ip, vp]
     L.orbb200_debug_blurred_level.argtypes = [vp, ip, ip, vp, ip]
@@ -68,6 +70,8 @@ def lib():
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
+    L.orbb200_stereo_match_batch.argtypes = [vp, ip, fp, fp, vp, vp, vp]
+    L.orbb200_stereo_match_batch_device.argtypes = [vp, ip, fp, fp, vp, vp, vp]
     L.orbb200_popc_peak.argtypes = [ip, C.POINTER(C.c_double)]
     _lib = L
     return L
@@ -166,6 +170,17 @@ class ORBextractor:
         check(self.L.orbb200_extract_batch_device(self.h, imgs_ptr, batch, width, height, stride, image_stride,
                                                   kps_ptr, desc_ptr, cap, n_ptr))
 
+    def stereo_match_batch(self, npairs, bf, b):
+        """Frame::ComputeStereoMatches for the pairs (image 2p, 2p+1) of the last extract_batch call (host outputs)."""
+        uR = np.zeros((npairs, self.cap), np.float32)
+        depth = np.zeros((npairs, self.cap), np.float32)
+        nv = np.zeros(npairs, np.int32)
+        check(self.L.orbb200_stereo_match_batch(self.h, npairs, bf, b, _p(uR), _p(depth), _p(nv)))
+        return uR, depth, nv
+
+    def stereo_match_batch_device(self, npairs, bf, b, uR_ptr, depth_ptr, nv_ptr):
+        check(self.L.orbb200_stereo_match_batch_device(self.h, npairs, bf, b, uR_ptr, depth_ptr, nv_ptr))
+
     def stream(self):
         return self.L.orbb200_extractor_stream(self.h)
 
@@ -179,6 +194,13 @@ class ORBextractor:
         ms = np.zeros(5, np.float32)
         check(self.L.orbb200_extractor_stage_ms(self.h, _p(ms), 5))
         return dict(zip(self.STAGES, ms.tolist()))
+
+    def stage_ms_sum(self):
+        """(dict of summed stage ms, number of calls covered) since set_profiling(True)."""
+        ms = np.zeros(5, np.float32)
+        n = C.c_int()
+        check(self.L.orbb200_extractor_stage_ms_sum(self.h, _p(ms), 5, C.byref(n)))
+        return dict(zip(self.STAGES, ms.tolist())), n.value
 
     def last_launches(self):
         return self.L.orbb200_extractor_last_launches(self.h)

@@ -105,3 +105,23 @@ def test_stereo_match_equals_oracle(configs):
     assert rn > 200, rn
     assert nvalid == rn
     assert np.array_equal(uR[:n], ruR) and np.array_equal(depth[:n], rdepth)
+
+
+def test_stereo_match_batch_equals_single(configs):
+    """batched F1 (pairs interleaved in one extract_batch call) == the two-handle single-pair call."""
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    bf, fx = 386.1448, 718.856
+    b = bf / fx
+    pairs = [synth.stereo_pair(w, h, 1100 + k) for k in range(3)]
+    imgs = np.stack([im for p in pairs for im in p])
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kps, desc, n = ex.extract_batch(imgs)
+    uR, depth, nv = ex.stereo_match_batch(3, bf, b)
+    for p in range(3):
+        exL, exR = orbb200.ORBextractor(nf, sfac, nl, ini, mn), orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+        kL, _ = exL(pairs[p][0])
+        exR(pairs[p][1])
+        suR, sdepth, snv = orbb200.stereo_match(exL, exR, bf, b)
+        nL = len(kL)
+        assert nL == n[2 * p] and snv == nv[p] and snv > 200
+        assert np.array_equal(uR[p, :nL], suR[:nL]) and np.array_equal(depth[p, :nL], sdepth[:nL])
