@@ -362,12 +362,11 @@ def bench_match(args, rank, world, dev, barrier, max_over_ranks):
     import synth
     L = orbb200.lib()
     q, db, _ = synth.descriptor_db(NQ, NDB, seed=7)
-    per = NDB // world
-    lo = rank * per
+    lo, hi = orbb200.shard_range(NDB, world, rank)
+    per = hi - lo
     q_d = torch.from_numpy(q).to(dev)
     db_d = torch.from_numpy(np.ascontiguousarray(db[lo:lo + per])).to(dev)
     part_d = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
-    gath_d = torch.empty((world, NQ, 4), dtype=torch.int32, device=dev)
     out_d = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
     ts = torch.cuda.Stream(device=dev)  # a real (non-default) stream: kernels, NCCL and events all order on it
     torch.cuda.set_stream(ts)
@@ -376,7 +375,7 @@ def bench_match(args, rank, world, dev, barrier, max_over_ranks):
     def step():
         orbb200.check(L.orbb200_match_bruteforce_top2_device(q_d.data_ptr(), NQ, db_d.data_ptr(), per, part_d.data_ptr(), lo, st))
         if world > 1:
-            dist.all_gather_into_tensor(gath_d, part_d)
+            gath_d = orbb200.gather_top2_parts(part_d)
             orbb200.check(L.orbb200_merge_top2_device(gath_d.data_ptr(), world, NQ, out_d.data_ptr(), st))
 
     for _ in range(3):

@@ -52,6 +52,12 @@ void orbb200_extractor_destroy(orbb200_extractor *e);
 int orbb200_level_tables(const orbb200_extractor *e, float *scale, float *inv_scale, float *sigma2, float *inv_sigma2,
                          int *nfeat);
 
+/* the same tables without a handle or a GPU (host arithmetic only): mvScaleFactor, mvInvScaleFactor, mvLevelSigma2,
+ * mvInvLevelSigma2, mnFeaturesPerLevel (nlevels entries each) and umax[16] (src/ORBextractor.cc:441-461, 468-493,
+ * 510-533).  Any output pointer may be NULL. */
+int orbb200_compute_level_tables(int nfeatures, float scaleFactor, int nlevels, float *scale, float *inv_scale,
+                                 float *sigma2, float *inv_sigma2, int *nfeat, int *umax);
+
 /* upper bound on keypoints per image for this handle (DistributeOctTree can exceed the per-level quota by
  * up to 3 nodes: src/ORBextractor.cc:879).  Use it to size kps/desc. */
 int orbb200_max_keypoints(const orbb200_extractor *e);
@@ -126,6 +132,12 @@ int orbb200_match_bruteforce_top2_device(const uint8_t *q_d, int nq, const uint8
  * SearchForTriangulation (:768-815), Fuse (:960-1003), SearchBySim3 (:1268-1283). */
 int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets,
                              const int *cand_idx, orbb200_top2 *out, int device);
+
+/* every distance of the same CSR candidate set: dist[c] = H(q[i], t[cand_idx[c]]) for cand_offsets[i] <= c <
+ * cand_offsets[i+1].  For the searches whose best/second-best loop skips targets claimed earlier in the same call
+ * (src/ORBmatcher.cc:93-95, 222, 475, 622, 1485-1487, 1624): the host replays the ordered loop on these distances. */
+int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets,
+                                const int *cand_idx, uint16_t *dist, int device);
 
 /* merge of per-shard top-2 results (config 5, database sharded by rows; shard s's indices already global):
  * parts[s*nq + i]; ties on best_dist go to the lowest shard (= lowest global index, first-seen rule). */

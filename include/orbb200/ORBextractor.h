@@ -1,0 +1,175 @@
+/*
+ * ORBextractor.h -- source-compatible replacement of ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:53-135)
+ * over the C-ABI of liborbb200.so (include/orbb200.h).  Header-only host C++; link with -lorbb200.
+ *
+ * Same constructor (nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST), same operator()(image, mask, keypoints,
+ * descriptors), same accessors, same public mvImagePyramid -- so Frame::ExtractORB (src/Frame.cc:285-292),
+ * Frame::Frame (:73-79) and Tracking::Tracking (src/Tracking.cc:118-130) compile unchanged.
+ *
+ * Behaviour kept from the reference:
+ *   - empty image: return with the outputs untouched (src/ORBextractor.cc:1264);
+ *   - the mask is ignored;  image must be CV_8UC1 (:1269, an assert there; an error line + 0 keypoints here);
+ *   - keypoints are cleared then filled, descriptors is created N x 32 CV_8U or released when N == 0 (:1288-1298);
+ *   - no exceptions, no return code: a CUDA failure prints one line to std::cerr and yields 0 keypoints, so that
+ *     Frame::Frame takes its `if(mvKeys.empty()) return;` exit (src/Frame.cc:89).
+ * There is no CPU fallback.
+ *
+ * Extensions (do not exist in the reference; defaults keep its behaviour):
+ *   SetDevice(int)               choose the GPU before the first call (default: current device)
+ *   SetPyramidMode(mode)         PYRAMID_EAGER (default): mvImagePyramid is downloaded after every call, because
+ *                                Frame::ComputeStereoMatches reads it (src/Frame.cc:584,674,686,691);
+ *                                PYRAMID_NONE: leave it empty (use orbb200::ComputeStereoMatches on the device instead)
+ *   Handle()                     the underlying orbb200_extractor*
+ */
+#ifndef ORBB200_ORBEXTRACTOR_H
+#define ORBB200_ORBEXTRACTOR_H
+
+#include <iostream>
+#include <list>
+#include <vector>
+
+#ifdef ORBB200_USE_OPENCV
+#include <opencv2/core/core.hpp>
+#else
+#include "cv_shim.h"
+#endif
+#include "../orbb200.h"
+
+namespace ORB_SLAM2 {
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+    enum PyramidMode { PYRAMID_EAGER = 0, PYRAMID_NONE = 1 };
+
+    ORBextractor(int nfeatures_, float scaleFactor_, int nlevels_, int iniThFAST_, int minThFAST_)
+        : nfeatures(nfeatures_), scaleFactor(scaleFactor_), nlevels(nlevels_), iniThFAST(iniThFAST_), minThFAST(minThFAST_),
+          handle_(nullptr), device_(-1), pyramidMode_(PYRAMID_EAGER)
+    {
+        static_assert(sizeof(cv::KeyPoint) == sizeof(orbb200_keypoint), "cv::KeyPoint must be the 28-byte POD");
+        mvScaleFactor.resize(nlevels);
+        mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels);
+        mvInvLevelSigma2.resize(nlevels);
+        mnFeaturesPerLevel.resize(nlevels);
+        umax.resize(16);
+        if (orbb200_compute_level_tables(nfeatures, scaleFactor_, nlevels, mvScaleFactor.data(), mvInvScaleFactor.data(),
+                                         mvLevelSigma2.data(), mvInvLevelSigma2.data(), mnFeaturesPerLevel.data(), umax.data()))
+            std::cerr << "ORBextractor: " << orbb200_last_error() << std::endl;
+        mvImagePyramid.resize(nlevels);
+    }
+
+    ~ORBextractor() { orbb200_extractor_destroy(handle_); } /* the reference never deletes its extractors; harmless */
+
+    ORBextractor(const ORBextractor &) = delete;
+    ORBextractor &operator=(const ORBextractor &) = delete;
+
+    // Compute the ORB features and descriptors on an image.  Mask is ignored (as in the reference).
+    void operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint> &_keypoints,
+                    cv::OutputArray _descriptors)
+    {
+        const cv::Mat image = _image.getMat();
+        if (image.empty()) return; // :1264
+        _keypoints.clear();
+        if (image.type() != CV_8UC1) { fail("image must be CV_8UC1", _descriptors); return; }
+        if (!ensure_handle()) { fail(orbb200_last_error(), _descriptors); return; }
+        const int cap = orbb200_max_keypoints(handle_);
+        _keypoints.resize(cap);
+        descBuf_.resize((size_t)cap * 32);
+        int n = 0;
+        const int rc = orbb200_extract(handle_, image.data, image.cols, image.rows, (int)image.step,
+                                       reinterpret_cast<orbb200_keypoint *>(_keypoints.data()), descBuf_.data(), cap, &n);
+        if (rc != ORBB200_OK) { _keypoints.clear(); fail(orbb200_last_error(), _descriptors); return; }
+        _keypoints.resize(n);
+        if (n == 0) {
+            _descriptors.release();
+        } else {
+            _descriptors.create(n, 32, CV_8U);
+            cv::Mat d = _descriptors.getMat();
+            for (int i = 0; i < n; i++) std::memcpy(d.ptr(i), descBuf_.data() + (size_t)i * 32, 32);
+        }
+        if (pyramidMode_ == PYRAMID_EAGER) download_pyramid();
+    }
+
+    int inline GetLevels() { return nlevels; }
+    float inline GetScaleFactor() { return (float)scaleFactor; }
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    std::vector<cv::Mat> mvImagePyramid;
+
+    /* ---- extensions -------------------------------------------------------------------------------- */
+    void SetDevice(int device) { device_ = device; }
+    void SetPyramidMode(PyramidMode m) { pyramidMode_ = m; }
+    orbb200_extractor *Handle() { ensure_handle(); return handle_; }
+    const std::vector<int> &GetFeaturesPerLevel() const { return mnFeaturesPerLevel; }
+
+protected:
+    bool ensure_handle()
+    {
+        if (handle_) return true;
+        return orbb200_extractor_create(&handle_, nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, device_) == ORBB200_OK;
+    }
+    void fail(const char *msg, cv::OutputArray d)
+    {
+        std::cerr << "ORBextractor (orbb200): " << msg << std::endl;
+        d.release();
+    }
+    void download_pyramid()
+    {
+        for (int l = 0; l < nlevels; l++) {
+            int w = 0, h = 0;
+            if (orbb200_pyramid_level(handle_, 0, l, nullptr, 0, &w, &h)) return;
+            mvImagePyramid[l].create(h, w, CV_8UC1);
+            orbb200_pyramid_level(handle_, 0, l, mvImagePyramid[l].data, (int)mvImagePyramid[l].step, &w, &h);
+        }
+    }
+
+    int nfeatures;
+    double scaleFactor;
+    int nlevels;
+    int iniThFAST;
+    int minThFAST;
+    std::vector<int> mnFeaturesPerLevel;
+    std::vector<int> umax;
+    std::vector<float> mvScaleFactor;
+    std::vector<float> mvInvScaleFactor;
+    std::vector<float> mvLevelSigma2;
+    std::vector<float> mvInvLevelSigma2;
+
+    orbb200_extractor *handle_;
+    int device_;
+    PyramidMode pyramidMode_;
+    std::vector<unsigned char> descBuf_;
+};
+
+} // namespace ORB_SLAM2
+
+namespace orbb200 {
+
+/* Device replacement of Frame::ComputeStereoMatches (src/Frame.cc:577-751): uses the device-resident pyramids and
+ * outputs of the last operator() call of both extractors.  mvuRight / mvDepth get N = #left keypoints entries
+ * (-1 where unmatched), exactly what the reference leaves in Frame::mvuRight / mvDepth.  Returns the match count
+ * (or -1 on error, after printing it). */
+inline int ComputeStereoMatches(ORB_SLAM2::ORBextractor &left, ORB_SLAM2::ORBextractor &right, int nLeft, float mbf, float mb,
+                                std::vector<float> &mvuRight, std::vector<float> &mvDepth)
+{
+    const int cap = orbb200_max_keypoints(left.Handle());
+    std::vector<float> u(cap > 0 ? cap : 1, -1.f), d(cap > 0 ? cap : 1, -1.f);
+    int nvalid = 0;
+    mvuRight.assign(nLeft, -1.0f);
+    mvDepth.assign(nLeft, -1.0f);
+    if (nLeft == 0) return 0;
+    if (orbb200_stereo_match(left.Handle(), right.Handle(), mbf, mb, u.data(), d.data(), &nvalid) != ORBB200_OK) {
+        std::cerr << "ComputeStereoMatches (orbb200): " << orbb200_last_error() << std::endl;
+        return -1;
+    }
+    for (int i = 0; i < nLeft && i < cap; i++) { mvuRight[i] = u[i]; mvDepth[i] = d[i]; }
+    return nvalid;
+}
+
+} // namespace orbb200
+
+#endif /* ORBB200_ORBEXTRACTOR_H */

@@ -1,0 +1,259 @@
+/*
+ * ORBmatcher.h -- ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:38-100, src/ORBmatcher.cc) with the
+ * descriptor-distance arithmetic of the searches on the GPU through the C-ABI (include/orbb200.h).
+ *
+ * Shape of every search: candidate generation -> DescriptorDistance per (query, candidate) ->
+ * running best / second-best -> accept test -> ordered side effect -> rotation-histogram cull.
+ * Here: a host prologue enumerates candidates with the caller's own, unchanged Frame::GetFeaturesInArea /
+ * FeatureVector walk and packs descriptors; ONE call to orbb200_candidate_distances computes every distance on the
+ * device; a host epilogue replays the reference loop in query order on those distances, so skip-if-claimed rules
+ * (src/ORBmatcher.cc:93-95, 222), strict '<' tie-breaking, thresholds, ratio test and the histogram are the
+ * reference's, statement for statement.
+ *
+ * The Search* members are templates over the caller's Frame / KeyFrame / MapPoint types: included in the reference
+ * tree they bind to ORB_SLAM2::Frame etc. (same member names: mvKeysUn, mDescriptors, mvpMapPoints, mFeatVec, ...),
+ * and this repo's tests bind them to small stand-ins (tests/cpp/facade_match.cpp).  Methods not listed here
+ * (SearchForInitialization, SearchBySim3, Fuse, the other SearchByProjection overloads) follow the same three steps
+ * over orbb200_candidate_distances / orbb200_match_candidates; see INTEGRATION.md 4.
+ */
+#ifndef ORBB200_ORBMATCHER_H
+#define ORBB200_ORBMATCHER_H
+
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <iostream>
+#include <type_traits>
+#include <vector>
+
+#ifdef ORBB200_USE_OPENCV
+#include <opencv2/core/core.hpp>
+#else
+#include "cv_shim.h"
+#endif
+#include "../orbb200.h"
+
+namespace ORB_SLAM2 {
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri), device_(-1) {}
+
+    // Hamming distance of two 32-byte descriptors (src/ORBmatcher.cc:1733-1749).  A single pair stays on the host.
+    static int DescriptorDistance(const cv::Mat &a, const cv::Mat &b)
+    {
+        const uint32_t *pa = a.ptr<uint32_t>(), *pb = b.ptr<uint32_t>();
+        int dist = 0;
+        for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
+        return dist;
+    }
+
+    // Track local map (src/ORBmatcher.cc:48-136; caller src/Tracking.cc:1463).
+    template <class FrameT, class MapPointT>
+    int SearchByProjection(FrameT &F, const std::vector<MapPointT *> &vpMapPoints, const float th = 3)
+    {
+        const bool bFactor = th != 1.0;
+        // prologue: queries in reference order with their windows
+        std::vector<int> qMP;                 // index into vpMapPoints
+        std::vector<float> qR;                // r * scale[level]
+        std::vector<int> offs(1, 0), cand;
+        std::vector<unsigned char> qDesc;
+        for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++) {
+            MapPointT *pMP = vpMapPoints[iMP];
+            if (!pMP->mbTrackInView) continue;
+            if (pMP->isBad()) continue;
+            const int nPredictedLevel = pMP->mnTrackScaleLevel;
+            float r = RadiusByViewingCos(pMP->mTrackViewCos);
+            if (bFactor) r *= th;
+            const float win = r * F.mvScaleFactors[nPredictedLevel];
+            const std::vector<size_t> vIndices = F.GetFeaturesInArea(pMP->mTrackProjX, pMP->mTrackProjY, win, nPredictedLevel - 1, nPredictedLevel);
+            if (vIndices.empty()) continue;
+            qMP.push_back((int)iMP);
+            qR.push_back(win);
+            for (size_t k = 0; k < vIndices.size(); k++) cand.push_back((int)vIndices[k]);
+            offs.push_back((int)cand.size());
+            const cv::Mat d = pMP->GetDescriptor();
+            qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
+        }
+        std::vector<uint16_t> dist;
+        if (!distances(qDesc, (int)qMP.size(), F.mDescriptors, offs, cand, dist)) return 0;
+        // epilogue: the reference loop (:86-131) on precomputed distances
+        int nmatches = 0;
+        for (size_t q = 0; q < qMP.size(); q++) {
+            MapPointT *pMP = vpMapPoints[qMP[q]];
+            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t idx = (size_t)cand[c];
+                if (F.mvpMapPoints[idx])
+                    if (F.mvpMapPoints[idx]->Observations() > 0) continue;
+                if (F.mvuRight[idx] > 0) {
+                    const float er = std::fabs(pMP->mTrackProjXR - F.mvuRight[idx]);
+                    if (er > qR[q]) continue;
+                }
+                const int d = dist[c];
+                if (d < bestDist) {
+                    bestDist2 = bestDist; bestDist = d;
+                    bestLevel2 = bestLevel; bestLevel = F.mvKeysUn[idx].octave;
+                    bestIdx = (int)idx;
+                } else if (d < bestDist2) {
+                    bestLevel2 = F.mvKeysUn[idx].octave;
+                    bestDist2 = d;
+                }
+            }
+            if (bestDist <= TH_HIGH) {
+                if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+                F.mvpMapPoints[bestIdx] = pMP;
+                nmatches++;
+            }
+        }
+        return nmatches;
+    }
+
+    // Relocalisation / reference-keyframe tracking (src/ORBmatcher.cc:171-303; callers src/Tracking.cc:907, 1682).
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT *pKF, FrameT &F, std::vector<MapPointT *> &vpMapPointMatches)
+    {
+        const std::vector<MapPointT *> vpMapPointsKF = pKF->GetMapPointMatches();
+        vpMapPointMatches = std::vector<MapPointT *>(F.N, static_cast<MapPointT *>(NULL));
+        // prologue: merge-walk of the two feature vectors (:193-279); one query per keyframe feature with a good point
+        std::vector<int> qKF, offs(1, 0), cand;
+        std::vector<unsigned char> qDesc;
+        typename std::remove_reference<decltype(pKF->mFeatVec)>::type::const_iterator KFit = pKF->mFeatVec.begin(), KFend = pKF->mFeatVec.end();
+        typename std::remove_reference<decltype(F.mFeatVec)>::type::const_iterator Fit = F.mFeatVec.begin(), Fend = F.mFeatVec.end();
+        while (KFit != KFend && Fit != Fend) {
+            if (KFit->first == Fit->first) {
+                const std::vector<unsigned int> &vIndicesKF = KFit->second, &vIndicesF = Fit->second;
+                for (size_t iKF = 0; iKF < vIndicesKF.size(); iKF++) {
+                    const unsigned int realIdxKF = vIndicesKF[iKF];
+                    MapPointT *pMP = vpMapPointsKF[realIdxKF];
+                    if (!pMP) continue;
+                    if (pMP->isBad()) continue;
+                    qKF.push_back((int)realIdxKF);
+                    for (size_t iF = 0; iF < vIndicesF.size(); iF++) cand.push_back((int)vIndicesF[iF]);
+                    offs.push_back((int)cand.size());
+                    const unsigned char *d = pKF->mDescriptors.ptr((int)realIdxKF);
+                    qDesc.insert(qDesc.end(), d, d + 32);
+                }
+                KFit++;
+                Fit++;
+            } else if (KFit->first < Fit->first) {
+                KFit = pKF->mFeatVec.lower_bound(Fit->first);
+            } else {
+                Fit = F.mFeatVec.lower_bound(KFit->first);
+            }
+        }
+        std::vector<uint16_t> dist;
+        if (!distances(qDesc, (int)qKF.size(), F.mDescriptors, offs, cand, dist)) return 0;
+        // epilogue (:214-266, :282-300)
+        int nmatches = 0;
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        for (size_t q = 0; q < qKF.size(); q++) {
+            const int realIdxKF = qKF[q];
+            int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const int realIdxF = cand[c];
+                if (vpMapPointMatches[realIdxF]) continue;
+                const int d = dist[c];
+                if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdxF = realIdxF; }
+                else if (d < bestDist2) bestDist2 = d;
+            }
+            if (bestDist1 <= TH_LOW) {
+                if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                    vpMapPointMatches[bestIdxF] = vpMapPointsKF[realIdxKF];
+                    if (mbCheckOrientation) {
+                        float rot = pKF->mvKeysUn[realIdxKF].angle - F.mvKeys[bestIdxF].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back(bestIdxF);
+                    }
+                    nmatches++;
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i == ind1 || i == ind2 || i == ind3) continue;
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    vpMapPointMatches[rotHist[i][j]] = static_cast<MapPointT *>(NULL);
+                    nmatches--;
+                }
+            }
+        }
+        return nmatches;
+    }
+
+    void SetDevice(int device) { device_ = device; } /* extension: GPU used by the searches (default: current) */
+
+public:
+    static const int TH_LOW = 50;
+    static const int TH_HIGH = 100;
+    static const int HISTO_LENGTH = 30;
+
+protected:
+    // one device call for all (query, candidate) pairs of a search
+    bool distances(const std::vector<unsigned char> &qDesc, int nq, const cv::Mat &targets, const std::vector<int> &offs,
+                   const std::vector<int> &cand, std::vector<uint16_t> &dist)
+    {
+        dist.assign(cand.size() ? cand.size() : 1, 0);
+        if (nq == 0 || cand.empty()) return true;
+        const unsigned char *t = targets.ptr();
+        std::vector<unsigned char> packed;
+        if (!targets.isContinuous()) { // cv::Mat ROI: pack rows
+            packed.resize((size_t)targets.rows * 32);
+            for (int r = 0; r < targets.rows; r++) std::memcpy(&packed[(size_t)r * 32], targets.ptr(r), 32);
+            t = packed.data();
+        }
+        if (orbb200_candidate_distances(qDesc.data(), nq, t, targets.rows, offs.data(), cand.data(), dist.data(), device_) != ORBB200_OK) {
+            std::cerr << "ORBmatcher (orbb200): " << orbb200_last_error() << std::endl; // no CPU fallback: 0 matches
+            return false;
+        }
+        return true;
+    }
+
+    // src/ORBmatcher.cc:147-164
+    template <class KeyFrameT>
+    bool CheckDistEpipolarLine(const cv::KeyPoint &kp1, const cv::KeyPoint &kp2, const cv::Mat &F12, const KeyFrameT *pKF2)
+    {
+        const float a = kp1.pt.x * F12.at<float>(0, 0) + kp1.pt.y * F12.at<float>(1, 0) + F12.at<float>(2, 0);
+        const float b = kp1.pt.x * F12.at<float>(0, 1) + kp1.pt.y * F12.at<float>(1, 1) + F12.at<float>(2, 1);
+        const float c = kp1.pt.x * F12.at<float>(0, 2) + kp1.pt.y * F12.at<float>(1, 2) + F12.at<float>(2, 2);
+        const float num = a * kp2.pt.x + b * kp2.pt.y + c;
+        const float den = a * a + b * b;
+        if (den == 0) return false;
+        const float dsqr = num * num / den;
+        return dsqr < 3.84 * pKF2->mvLevelSigma2[kp2.octave];
+    }
+
+    // src/ORBmatcher.cc:138-144
+    float RadiusByViewingCos(const float &viewCos)
+    {
+        if (viewCos > 0.998) return 2.5;
+        else return 4.0;
+    }
+
+    // src/ORBmatcher.cc:1687-1728
+    void ComputeThreeMaxima(std::vector<int> *histo, const int L, int &ind1, int &ind2, int &ind3)
+    {
+        int max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < L; i++) {
+            const int s = (int)histo[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    }
+
+    float mfNNratio;
+    bool mbCheckOrientation;
+    int device_;
+};
+
+} // namespace ORB_SLAM2
+
+#endif /* ORBB200_ORBMATCHER_H */

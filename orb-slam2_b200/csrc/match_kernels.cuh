@@ -196,6 +196,20 @@ __global__ void k_match_candidates(const uint8_t *__restrict__ q, int nq, const 
     }
 }
 
+// all (query, candidate) distances of a CSR candidate set: dist[c] for every list entry c.  The host epilogues of
+// the Search* methods that skip targets claimed earlier in the same call (src/ORBmatcher.cc:93-95, 222, 1485-1487)
+// need every distance, not only the top-2.
+__global__ void k_candidate_distances(const uint8_t *__restrict__ q, int nq, const uint8_t *__restrict__ t,
+                                      const int *__restrict__ offs, const int *__restrict__ idx, unsigned short *__restrict__ dist)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= nq) return;
+    const Desc Q = load_desc(q + (size_t)warp * 32);
+    const int c0 = offs[warp], c1 = offs[warp + 1];
+    for (int c = c0 + lane; c < c1; c += 32)
+        dist[c] = (unsigned short)hamming(Q, load_desc(t + (size_t)__ldg(idx + c) * 32));
+}
+
 // POPC-pipe peak probe for the matching roofline: dependent-free popc chains, 8 per iteration.
 __global__ void k_popc_peak(unsigned int *out, int iters)
 {

@@ -158,6 +158,33 @@ int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt,
     return ORBB200_OK;
 }
 
+int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets, const int *cand_idx,
+                                uint16_t *dist, int device)
+{
+    if (nq <= 0) return ORBB200_OK;
+    ORB_ARG_OK(q && cand_offsets, "null pointer");
+    const int total = cand_offsets[nq];
+    if (total <= 0) return ORBB200_OK;
+    ORB_ARG_OK(t && cand_idx && dist && nt > 0, "candidates without targets");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dq, *dt, *dout, *doffs, *didx;
+    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)nt * 32, &dt)) ||
+        (rc = scratch_get(2, (size_t)total * 2, &dout)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
+        (rc = scratch_get(4, (size_t)total * 4, &didx)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
+    k_candidate_distances<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
+                                                               (const int *)didx, (unsigned short *)dout);
+    ORB_CUDA_OK(cudaMemcpyAsync(dist, dout, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
 int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream)
 {
     ORB_ARG_OK(parts_d && out_d && nshards > 0 && nq > 0, "bad arguments");

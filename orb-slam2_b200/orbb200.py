@@ -17,12 +17,12 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
 
 EXPORTS = [
-    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_max_keypoints",
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
-    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_merge_top2",
+    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
     "orbb200_stereo_match_batch_device", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
 ]
@@ -49,6 +49,7 @@ def lib():
     L.orbb200_extractor_destroy.argtypes = [vp]
     L.orbb200_extractor_destroy.restype = None
     L.orbb200_level_tables.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbb200_compute_level_tables.argtypes = [ip, fp, ip, vp, vp, vp, vp, vp, vp]
     L.orbb200_max_keypoints.argtypes = [vp]
     L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]
@@ -67,6 +68,7 @@ def lib():
     L.orbb200_match_bruteforce_top2.argtypes = [vp, ip, vp, ip, vp, ip]
     L.orbb200_match_bruteforce_top2_device.argtypes = [vp, ip, vp, ip, vp, ip, vp]
     L.orbb200_match_candidates.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
+    L.orbb200_candidate_distances.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
@@ -263,6 +265,15 @@ class ORBmatcher:
         check(self.L.orbb200_match_candidates(_p(q), len(q), _p(t), len(t), _p(offsets), _p(idx), _p(out), self.device))
         return out
 
+    def candidate_distances(self, q, t, offsets, idx):
+        q = np.ascontiguousarray(q, np.uint8)
+        t = np.ascontiguousarray(t, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        idx = np.ascontiguousarray(idx, np.int32)
+        out = np.zeros(max(int(offsets[-1]), 1), np.uint16)
+        check(self.L.orbb200_candidate_distances(_p(q), len(q), _p(t), len(t), _p(offsets), _p(idx), _p(out), self.device))
+        return out[:int(offsets[-1])]
+
     def merge_top2(self, parts):
         parts = np.ascontiguousarray(parts, TOP2_DTYPE)
         ns, nq = parts.shape
@@ -286,3 +297,23 @@ def stereo_match(left, right, bf, b):
     nv = C.c_int()
     check(lib().orbb200_stereo_match(left.h, right.h, bf, b, _p(uR), _p(depth), C.byref(nv)))
     return uR, depth, nv.value
+
+
+# ---- multi-GPU host logic: frames and database rows are sharded per rank --------------------------
+def shard_range(n, world, rank):
+    """contiguous [lo, hi) slice of n units owned by `rank` of `world` (first n % world ranks get one more)"""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_top2_parts(part, group=None):
+    """all-gather of the per-shard top-2 records (config 5's only exchange step): part is a torch int32 tensor
+    [nq, 4] (best_dist, best_idx GLOBAL, second_dist, second_idx GLOBAL) on the rank's device (NCCL) or on the CPU
+    (gloo); returns [world, nq, 4] ordered by rank = by database position, which the merge's first-seen rule needs."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    out = torch.empty((world * part.shape[0],) + tuple(part.shape[1:]), dtype=part.dtype, device=part.device)
+    dist.all_gather_into_tensor(out, part.contiguous(), group=group)  # concatenation along dim 0, rank order
+    return out.view((world,) + tuple(part.shape))

@@ -1,0 +1,92 @@
+"""GPU: the host C++ facade (include/orbb200/ORBextractor.h), driven the way Frame::Frame / Frame::ExtractORB drive
+the reference class (src/Frame.cc:73-94, 285-292), against the CPU oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import orbb200
+import ref_cpu
+import synth
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "orb-slam2_b200", "facade_extract.bin")
+
+
+def _run(tmp_path, left, right, params, stereo_args=()):
+    h, w = left.shape
+    lp, rp = str(tmp_path / "l.raw"), str(tmp_path / "r.raw")
+    left.tofile(lp)
+    if right is not None:
+        right.tofile(rp)
+    out = str(tmp_path / "o")
+    nf, sfac, nl, ini, mn = params
+    cmd = [EXE, str(w), str(h), str(nf), repr(sfac), str(nl), str(ini), str(mn), lp, rp if right is not None else "-", out]
+    cmd += [repr(float(a)) for a in stereo_args]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr + r.stdout
+    kps = np.fromfile(out + "_kps.bin", orbb200.KP_DTYPE)
+    desc = np.fromfile(out + "_desc.bin", np.uint8).reshape(-1, 32)
+    return out, kps, desc, r.stdout
+
+
+def test_facade_mono_equals_oracle(tmp_path, configs):
+    assert os.path.exists(EXE), "facade_extract.bin not built: run __graft_entry__.build()"
+    w, h, nf, sfac, nl, ini, mn = configs["tum"]
+    img = synth.textured_frame(w, h, 1000)
+    out, kps, desc, _ = _run(tmp_path, img, None, (nf, sfac, nl, ini, mn))
+    ref = ref_cpu.RefExtractor(nf, sfac, nl, ini, mn)
+    kc, dc = ref.extract(img)
+    assert len(kps) == len(kc)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(kps[f], kc[f]), f
+    assert np.abs(kps["angle"] - kc["angle"]).max() < 0.0058
+    assert (desc != dc).any(axis=1).mean() <= 0.001
+    # accessors == constructor tables of the reference (ORBextractor.cc:441-461)
+    tabs = np.fromfile(out + "_tables.bin", np.float32)
+    tb = ref.tables()
+    assert tabs[0] == nl and tabs[1] == np.float32(sfac)
+    got = tabs[2:].reshape(4, nl)
+    for row, key in zip(got, ("scale", "inv_scale", "sigma2", "inv_sigma2")):
+        assert np.array_equal(row, tb[key]), key
+    # public mvImagePyramid (ORBextractor.h:100)
+    for l in range(nl):
+        lw, lh = ref.level_size(l)
+        assert np.array_equal(np.fromfile(out + "_pyr%d.bin" % l, np.uint8).reshape(lh, lw), ref.level_image(l)), l
+
+
+def test_facade_stereo_two_threads_and_stereo_matches(tmp_path, configs):
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    left, right = synth.stereo_pair(w, h, 1001)
+    bf, fx = 386.1448, 718.856
+    out, kps, desc, stdout = _run(tmp_path, left, right, (nf, sfac, nl, ini, mn), (bf, bf / fx))
+    eL, eR = ref_cpu.RefExtractor(nf, sfac, nl, ini, mn), ref_cpu.RefExtractor(nf, sfac, nl, ini, mn)
+    kL, dL = eL.extract(left)
+    kR, dR = eR.extract(right)
+    kpsR = np.fromfile(out + "_kpsR.bin", orbb200.KP_DTYPE)
+    for f in ("x", "y", "octave", "response"):
+        assert np.array_equal(kps[f], kL[f]) and np.array_equal(kpsR[f], kR[f]), f
+    # the oracle's stereo matcher on the GPU's own keypoints/descriptors (descriptors may differ in <=0.1 % rows)
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kLg, dLg = ex(left)
+    kRg, dRg = orbb200.ORBextractor(nf, sfac, nl, ini, mn)(right)
+    pyrL = [eL.level_image(l) for l in range(nl)]
+    pyrR = [eR.level_image(l) for l in range(nl)]
+    tb = eL.tables()
+    ruR, rdepth, _, rn = ref_cpu.stereo_match(kLg, dLg, kRg, dRg, pyrL, pyrR, tb["scale"], tb["inv_scale"], bf, bf / fx)
+    uR = np.fromfile(out + "_uright.bin", np.float32)
+    depth = np.fromfile(out + "_depth.bin", np.float32)
+    assert len(uR) == len(kps) and ("stereo_matches %d" % rn) in stdout
+    assert np.array_equal(uR, ruR) and np.array_equal(depth, rdepth)
+
+
+def test_facade_matcher_templates_equal_reference_loops():
+    """ORBmatcher::SearchByProjection(F, MapPoints, th) and SearchByBoW(KF, F) of include/orbb200/ORBmatcher.h bound to
+    stand-in Frame/KeyFrame/MapPoint types vs the sequential reference loops with the oracle's DescriptorDistance."""
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_match.bin")
+    assert os.path.exists(exe), "facade_match.bin not built: run __graft_entry__.build()"
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.count("ok ") == 3 and "FAIL" not in r.stdout, r.stdout + r.stderr
