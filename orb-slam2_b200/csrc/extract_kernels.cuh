@@ -258,128 +258,7 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ Ex
     }
 }
 
-// ---------------------------------------------------------------------------------------------------
-// E3+E4  fast_cells: one thread block per 30-px grid cell of any level (src/ORBextractor.cc:953-1006).
-//   cv::FAST(roi, th, nms=true) semantics, derived in DESIGN.md:
-//     score S(p) = max over the 16 contiguous 9-arcs of min|v - ring| - 1 (threshold independent);
-//     corner at th  <=>  S >= th;   NMS keeps p iff S(p) > S(q) for the 8 neighbours q, where q outside the
-//     ROI interior or not a corner at th counts 0.  For S(p) >= th the masked comparison equals the raw
-//     one, so the survivors at iniTh are the local maxima with S >= iniTh and the minTh retry (taken only
-//     when that set is empty) yields the local maxima with S >= minTh -- one scoring pass serves both.
-//   The ROI interiors tile [19, W-19) x [19, H-19) without overlap, so every pixel is scored exactly once.
-//   Output: the cell's candidates in row-major order in its fixed slot + the count.
-// ---------------------------------------------------------------------------------------------------
-constexpr int FC_THREADS = 128;
-constexpr int FC_SP = 96;   // staged ROI row: <= 15 (alignment) + 66 (ROI) bytes
-constexpr int FC_ROWS = 66; // hCell + 6 <= 66 (hCell < 60 because nRows = floor(height/30))
-constexpr int FC_SCP = 64;  // score row pitch: interior <= 60 wide + zero border
-
-// strength M of the FAST-9 test at a pixel: corner at threshold t  <=>  M > t.  c points into shared memory.
-__device__ __forceinline__ int fast_arc_strength(const uint8_t *c, int th)
-{
-    const int v = c[0];
-    int d[16];
-    d[0] = v - c[3 * FC_SP];       d[8] = v - c[-3 * FC_SP];
-    d[4] = v - c[3];               d[12] = v - c[-3];
-    // quick reject: every 9-arc contains k or k+8 for each k
-    bool br = ((d[0] > th) | (d[8] > th)) & ((d[4] > th) | (d[12] > th));
-    bool dk = ((d[0] < -th) | (d[8] < -th)) & ((d[4] < -th) | (d[12] < -th));
-    if (!(br | dk)) return 0;
-    d[2] = v - c[2 * FC_SP + 2];   d[10] = v - c[-2 * FC_SP - 2];
-    d[6] = v - c[-2 * FC_SP + 2];  d[14] = v - c[2 * FC_SP - 2];
-    br = br & ((d[2] > th) | (d[10] > th)) & ((d[6] > th) | (d[14] > th));
-    dk = dk & ((d[2] < -th) | (d[10] < -th)) & ((d[6] < -th) | (d[14] < -th));
-    if (!(br | dk)) return 0;
-    d[1] = v - c[3 * FC_SP + 1];   d[9] = v - c[-3 * FC_SP - 1];
-    d[3] = v - c[FC_SP + 3];       d[11] = v - c[-FC_SP - 3];
-    d[5] = v - c[-FC_SP + 3];      d[13] = v - c[FC_SP - 3];
-    d[7] = v - c[-3 * FC_SP + 1];  d[15] = v - c[3 * FC_SP - 1];
-    // sliding 9-window min and max over the circular 16-array with 3-input min/max (VIMNMX3)
-    int mn3[16], mx3[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        mn3[k] = __vimin3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        mx3[k] = __vimax3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-    }
-    // NOTE: keep the two reductions separate and negate once at the end.  ptxas 12.9 (sm_100a) miscompiles
-    // max(best, mn9, -mx9) -- it folds the negation into VIMNMX3 and drops it (verified on a B200 with
-    // tools/scratch/vimnmx.cu: even the plain-loop form returns max(d) instead of the arc strength).
-    int bmn = 0, bmx = 0x7fffffff;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int mn9 = __vimin3_s32(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
-        const int mx9 = __vimax3_s32(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-        bmn = max(bmn, mn9);
-        bmx = min(bmx, mx9);
-    }
-    return max(bmn, -bmx);
-}
-
-__global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant__ ExtractParams P)
-{
-    __shared__ __align__(16) uint8_t sImg[FC_ROWS * FC_SP];
-    __shared__ uint8_t sSc[(FC_ROWS - 6 + 2) * FC_SCP];
-    __shared__ int scanTmp[34];
-    const int c = blockIdx.x, b = blockIdx.y;
-    int l = 0;
-    while (l + 1 < P.nlevels && c >= P.geom[l + 1].cellBase) l++;
-    const LevelGeom g = P.geom[l];
-    const int cc = c - g.cellBase, ci = cc / g.nCols, cj = cc - ci * g.nCols;
-    const int maxBX = g.w - 16, maxBY = g.h - 16;
-    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
-    const int maxY = min(iniY + g.hCell + 6, maxBY), maxX = min(iniX + g.wCell + 6, maxBX);
-    const int rw = maxX - iniX, rh = maxY - iniY;
-    int *cellCount = P.cellCount + (size_t)b * P.totalCells + c;
-    if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || rw < 7 || rh < 7) { // skipped cell (:957-976) or empty interior
-        if (threadIdx.x == 0) *cellCount = 0;
-        return;
-    }
-    int pitch, valid;
-    const uint8_t *img = level_ptr(P, g, l, b, pitch, valid);
-    const int xb = iniX & ~15;
-    const int nbytes = ((maxX - xb) + 15) & ~15;
-    load_tile(sImg, FC_SP, img, pitch, valid, g.w, xb, nbytes, iniY, rh);
-    for (int i = threadIdx.x; i < (FC_ROWS - 4) * FC_SCP / 4; i += FC_THREADS) reinterpret_cast<int *>(sSc)[i] = 0;
-    __syncthreads();
-    const int iw = rw - 6, ih = rh - 6, npx = iw * ih;
-    const int minTh = P.minTh, iniTh = P.iniTh;
-    const uint8_t *org = sImg + 3 * FC_SP + (iniX - xb) + 3;
-    for (int p = threadIdx.x; p < npx; p += FC_THREADS) {
-        const int y = p / iw, x = p - y * iw;
-        const int M = fast_arc_strength(org + y * FC_SP + x, minTh);
-        if (M > minTh) sSc[(y + 1) * FC_SCP + x + 1] = (uint8_t)(M - 1);
-    }
-    __syncthreads();
-    // local maxima, emitted in row-major order: thread t owns pixels [t*chunk, (t+1)*chunk)
-    const int chunk = (npx + FC_THREADS - 1) / FC_THREADS; // <= 29
-    const int p0 = threadIdx.x * chunk, p1 = min(p0 + chunk, npx);
-    unsigned int lmMask = 0, iniMask = 0;
-    for (int p = p0; p < p1; p++) {
-        const int y = p / iw, x = p - y * iw;
-        const uint8_t *s = sSc + (y + 1) * FC_SCP + x + 1;
-        const int v = s[0];
-        if (v == 0) continue;
-        if (v > s[-1] && v > s[1] && v > s[-FC_SCP - 1] && v > s[-FC_SCP] && v > s[-FC_SCP + 1] && v > s[FC_SCP - 1] &&
-            v > s[FC_SCP] && v > s[FC_SCP + 1]) {
-            lmMask |= 1u << (p - p0);
-            if (v >= iniTh) iniMask |= 1u << (p - p0);
-        }
-    }
-    const int anyIni = __syncthreads_or(iniMask != 0);
-    const unsigned int mask = anyIni ? iniMask : lmMask;
-    int total;
-    int off = block_excl_scan(__popc(mask), scanTmp, &total);
-    uint32_t *out = P.cand + (size_t)b * P.candStride + g.candOff + (size_t)cc * g.cellCap;
-    unsigned int m = mask;
-    while (m) {
-        const int k = __ffs(m) - 1;
-        m &= m - 1;
-        const int p = p0 + k, y = p / iw, x = p - y * iw;
-        const int s = sSc[(y + 1) * FC_SCP + x + 1];
-        out[off++] = (uint32_t)(cj * g.wCell + x + 3) | ((uint32_t)(ci * g.hCell + y + 3) << 12) | ((uint32_t)s << 24);
-    }
-    if (threadIdx.x == 0) *cellCount = total;
-}
+// E3+E4 fast_cells: see fast_kernel.cuh
 
 #endif // ORBB200_EXTRACT_IMPL
 

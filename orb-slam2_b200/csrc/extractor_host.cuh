@@ -20,6 +20,7 @@ struct orbb200_extractor {
     size_t pyrStride = 0, candStride = 0, nodeWsStride = 0;
     int totalCells = 0, nodeTotal = 0, totalBlurTiles = 0, coefTotal = 0;
     size_t octreeSmem = 0;
+    int fastRows = 7; // staged ROI rows of the largest cell (k_fast_cells dynamic shared memory)
     // device buffers
     orbb200::LevelGeom *d_geom = nullptr;
     int *d_umax = nullptr;

@@ -9,6 +9,7 @@
 #define ORBB200_EXTRACT_IMPL
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
+#include "fast_kernel.cuh"
 #include "octree_kernel.cuh"
 
 namespace orbb200 {
@@ -100,6 +101,9 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
         e->totalBlurTiles = tileBase;
         e->coefTotal = coefOff;
         e->octreeSmem = octSmem;
+        e->fastRows = 7;
+        for (int l = 0; l < L; l++)
+            if (e->geom[l].nCells > 0) e->fastRows = std::min(std::max(e->fastRows, e->geom[l].hCell + 6), (int)FC_MAXROWS);
         if (octSmem > 200 * 1024) { set_error("nfeatures too large for the quadtree kernel's shared memory (%zu B)", octSmem); return ORBB200_ERR_ARG; }
         // cv::resize INTER_LINEAR tables (scale = 1/((double)dst/src), 11-bit coefficients)
         std::vector<int> xofs(coefOff, 0), yofs(coefOff, 0);
