@@ -10,6 +10,7 @@
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
 #include "fast_kernel.cuh"
+#include "stage_kernel.cuh"
 #include "octree_kernel.cuh"
 
 namespace orbb200 {

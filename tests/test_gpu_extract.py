@@ -121,3 +121,44 @@ def test_large_image_4k_properties():
     kc, dc = ref_cpu.RefExtractor(*params).extract(img)
     _compare(kg, dg, kc, dc)
     assert len(kg) >= 8000
+
+
+@pytest.mark.parametrize("layout", ["packed_odd_pitch", "misaligned_base", "aligned_pitch"])
+def test_device_api_equals_host_api(configs, layout):
+    """orbb200_extract_batch_device on device-resident images (the bench's `value` path), for aligned and unaligned
+    caller layouts (packed 1241-byte rows are staged once into the aligned pyramid slot), == the host-buffer API."""
+    import torch
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    B = 3
+    imgs = np.stack([synth.textured_frame(w, h, 3000 + k) for k in range(B)])
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kps_h, desc_h, n_h = ex.extract_batch(imgs)
+    if layout == "aligned_pitch":
+        pitch, off = 1248, 0
+    elif layout == "packed_odd_pitch":
+        pitch, off = w, 0
+    else:
+        pitch, off = w + 2, 3
+    img_stride = pitch * h + (13 if layout == "misaligned_base" else 0)
+    if layout == "aligned_pitch":
+        img_stride = (img_stride + 255) // 256 * 256
+    raw = torch.zeros(off + img_stride * B + 64, dtype=torch.uint8, device="cuda")
+    for b in range(B):
+        view = raw[off + b * img_stride: off + b * img_stride + pitch * h].view(h, pitch)
+        view[:, :w] = torch.from_numpy(imgs[b]).cuda()
+    cap = ex.cap
+    kps_d = torch.zeros((B, cap, 7), dtype=torch.float32, device="cuda")
+    desc_d = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    n_d = torch.zeros(B, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ex2 = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    ex2.extract_batch_device(raw.data_ptr() + off, B, w, h, pitch, img_stride, kps_d.data_ptr(), desc_d.data_ptr(), cap, n_d.data_ptr())
+    ex2.sync()
+    n = n_d.cpu().numpy()
+    assert np.array_equal(n, n_h)
+    kd = kps_d.cpu().numpy().view(np.uint8).reshape(B, cap, 28)
+    for b in range(B):
+        assert np.array_equal(kd[b, :n[b]], kps_h[b, :n[b]].view(np.uint8).reshape(-1, 28))
+        assert np.array_equal(desc_d[b, :n[b]].cpu().numpy(), desc_h[b, :n[b]])
+    for l in range(nl):
+        assert np.array_equal(ex2.pyramid_level(l, 1), ex.pyramid_level(l, 1)), l
