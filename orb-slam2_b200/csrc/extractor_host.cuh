@@ -36,8 +36,8 @@ struct orbb200_extractor {
     int outCap = 0, outBatch = 0;
     // batched stereo matcher scratch / outputs (orbb200_stereo_match_batch*)
     float *d_stU = nullptr, *d_stD = nullptr;
-    int *d_stSad = nullptr, *d_stN = nullptr;
-    size_t stElems = 0;
+    int *d_stSad = nullptr, *d_stN = nullptr, *d_stRows = nullptr;
+    size_t stElems = 0, stRowElems = 0;
     int stPairs = 0;
     // last call
     int lastBatch = 0, lastCap = 0;

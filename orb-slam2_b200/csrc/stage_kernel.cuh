@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(ST_THREADS) k_stage_level0(const uint8_t *__re
         uint4 out = make_uint4(0, 0, 0, 0);
         if (x < w) {
             const uint8_t *a = simg + (size_t)row * srcPitch + x;
-            const uint8_t *last = min(a + 15, simg + (size_t)row * srcPitch + (w - 1)); // last needed byte
+            const uint8_t *last = a + min(15, w - 1 - x); // last needed byte
             const size_t m = (size_t)a & 15;
             const uint8_t *a0 = a - m;
             unsigned int W[9];

@@ -41,6 +41,9 @@ struct StereoParams {
     float sf[ORBB200_MAX_LEVELS], isf[ORBB200_MAX_LEVELS];
     float *uRight, *depth;
     int *sad; // SAD distance per left keypoint, -1 when no depth
+    // row buckets of the right keypoints (:594-604): rowStart[pair][nRows+1], rowList[pair][rowListStride]
+    int *rowStart, *rowList;
+    size_t rowListStride;
     size_t outStride; // per-pair stride of uRight / depth / sad
     int cap;          // keypoint capacity per image (counts are clamped to it)
 };
@@ -52,13 +55,58 @@ __device__ __forceinline__ const uint8_t *stereo_level(const StereoSide &s, cons
     return s.pyr + g.imgOff;
 }
 
+// Row buckets of the right keypoints (src/Frame.cc:594-604): keypoint iR is listed in every image row of
+// [floor(y - 2*scale[octave]), ceil(y + 2*scale[octave])].  One block per pair; counts and fill cursors live in
+// shared memory.  The order inside a row is not the reference's push_back order -- the matcher below takes the
+// lexicographic (distance, iR) minimum, which is order independent and equals the reference's first-wins scan of
+// a list sorted by iR.
+__global__ void __launch_bounds__(512) k_stereo_rows(const __grid_constant__ StereoParams P)
+{
+    extern __shared__ int srow[]; // [nRows] counts, then cursors
+    __shared__ int scanTmp[34];
+    const int pair = blockIdx.x, tid = threadIdx.x, NT = blockDim.x;
+    const StereoSide SR = stereo_side(P.R, pair);
+    const int nR = min(*SR.n, P.cap), nRows = P.nRows;
+    int *rowStart = P.rowStart + (size_t)pair * (nRows + 1);
+    int *rowList = P.rowList + (size_t)pair * P.rowListStride;
+    for (int r = tid; r < nRows; r += NT) srow[r] = 0;
+    __syncthreads();
+    for (int iR = tid; iR < nR; iR += NT) {
+        const orbb200_keypoint kR = SR.kps[iR];
+        const float r = __fmul_rn(2.0f, P.sf[kR.octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(kR.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kR.y, r)), 0);
+        for (int yi = minr; yi <= maxr; yi++) atomicAdd(&srow[yi], 1);
+    }
+    __syncthreads();
+    int run = 0;
+    for (int base = 0; base < nRows; base += NT) {
+        const int r = base + tid;
+        const int c = r < nRows ? srow[r] : 0;
+        int tot;
+        const int ex = block_excl_scan(c, scanTmp, &tot);
+        if (r < nRows) { rowStart[r] = run + ex; srow[r] = run + ex; }
+        run += tot;
+    }
+    if (tid == 0) rowStart[nRows] = run;
+    __syncthreads();
+    for (int iR = tid; iR < nR; iR += NT) {
+        const orbb200_keypoint kR = SR.kps[iR];
+        const float r = __fmul_rn(2.0f, P.sf[kR.octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(kR.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kR.y, r)), 0);
+        for (int yi = minr; yi <= maxr; yi++) {
+            const int pos = atomicAdd(&srow[yi], 1);
+            if ((size_t)pos < P.rowListStride) rowList[pos] = iR;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ StereoParams P)
 {
     const int lane = threadIdx.x & 31;
     const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int pair = blockIdx.y;
     const StereoSide SL = stereo_side(P.L, pair), SR = stereo_side(P.R, pair);
-    const int nL = min(*SL.n, P.cap), nR = min(*SR.n, P.cap);
+    const int nL = min(*SL.n, P.cap);
     if (iL >= nL) return;
     const orbb200_keypoint kL = SL.kps[iL];
     float uRight = -1.f, depth = -1.f;
@@ -73,15 +121,17 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
     t.d1 = 100; // bestDist starts at TH_HIGH (:633)
     if (row >= 0 && row < P.nRows && !(maxU < 0)) {
         const Desc dL = load_desc(SL.desc + (size_t)iL * 32);
-        for (int iR = lane; iR < nR; iR += 32) {
-            const orbb200_keypoint kR = SR.kps[iR];
-            const float r = __fmul_rn(2.0f, P.sf[kR.octave]);
-            const int maxr = (int)ceilf(__fadd_rn(kR.y, r)), minr = (int)floorf(__fsub_rn(kR.y, r));
-            if (row < minr || row > maxr) continue;
-            if (kR.octave < levelL - 1 || kR.octave > levelL + 1) continue;
-            if (kR.x >= minU && kR.x <= maxU) {
+        const int *rowStart = P.rowStart + (size_t)pair * (P.nRows + 1);
+        const int *rowList = P.rowList + (size_t)pair * P.rowListStride;
+        const int c0 = rowStart[row], c1 = min(rowStart[row + 1], (int)P.rowListStride);
+        for (int c = c0 + lane; c < c1; c += 32) {
+            const int iR = rowList[c];
+            const int octR = SR.kps[iR].octave;
+            if (octR < levelL - 1 || octR > levelL + 1) continue;
+            const float uR = SR.kps[iR].x;
+            if (uR >= minU && uR <= maxU) {
                 const int d = hamming(dL, load_desc(SR.desc + (size_t)iR * 32));
-                if (d < t.d1) { t.d1 = d; t.i1 = iR; }
+                if (d < t.d1 || (d == t.d1 && t.i1 >= 0 && iR < t.i1)) { t.d1 = d; t.i1 = iR; }
             }
         }
     }
@@ -168,18 +218,30 @@ __global__ void __launch_bounds__(1024) k_stereo_median(const __grid_constant__ 
     __syncthreads();
     const int n = s_cnt, k = n / 2;
     if (n == 0) { if (threadIdx.x == 0) *nValid = 0; return; }
-    // the k-th smallest value v: #(< v) <= k < #(<= v)
-    for (int i = threadIdx.x; i < nL; i += blockDim.x) {
-        const int v = sad[i];
-        if (v < 0) continue;
-        int lt = 0, le = 0;
-        for (int j = 0; j < nL; j++) {
-            const int u = sad[j];
-            if (u >= 0) { lt += u < v; le += u <= v; }
+    // k-th smallest SAD (0-based) by a two-level 256-bin histogram select (values < 2^16: 121 * 510)
+    __shared__ int hist[256];
+    __shared__ int s_bin, s_rank;
+    for (int pass = 0; pass < 2; pass++) {
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        for (int i = threadIdx.x; i < nL; i += blockDim.x) {
+            const int v = sad[i];
+            if (v < 0) continue;
+            if (pass == 0) atomicAdd(&hist[min(v >> 8, 255)], 1);
+            else if (min(v >> 8, 255) == s_bin) atomicAdd(&hist[v & 255], 1);
         }
-        if (lt <= k && k < le) s_median = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int rank = pass == 0 ? k : s_rank, bsel = 255;
+            for (int i = 0, acc = 0; i < 256; i++) {
+                if (acc + hist[i] > rank) { bsel = i; rank -= acc; break; }
+                acc += hist[i];
+            }
+            if (pass == 0) { s_bin = bsel; s_rank = rank; }
+            else s_median = (s_bin << 8) | bsel;
+        }
+        __syncthreads();
     }
-    __syncthreads();
     const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);
     int removed = 0;
     for (int i = threadIdx.x; i < nL; i += blockDim.x) {
