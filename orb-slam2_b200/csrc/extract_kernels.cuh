@@ -167,97 +167,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_pyramid_resize(const __grid_cons
     }
 }
 
-// ---------------------------------------------------------------------------------------------------
-// E7  blur7: cv::GaussianBlur 7x7 sigma 2, 8U fixed point (Q8 taps 18 34 48 56 48 34 18), REFLECT_101 at the
-//     level's own edges (src/ORBextractor.cc:1312-1314).  All levels in one launch through a tile table.
-//     Tile 128 x 32, 256 threads: horizontal pass u8 -> u16 in shared memory, vertical pass -> u8.
-// ---------------------------------------------------------------------------------------------------
-constexpr int BL_TW = 128, BL_TH = 32, BL_THREADS = 256;
-constexpr int BL_SP = BL_TW + 32; // staged row: 16-aligned start, 3-px halo each side
-
-__device__ __forceinline__ int reflect101(int p, int n)
-{
-    if (n == 1) return 0;
-    while (p < 0 || p >= n) p = p < 0 ? -p : 2 * (n - 1) - p;
-    return p;
-}
-
-__global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ ExtractParams P)
-{
-    __shared__ __align__(16) uint8_t sIn[(BL_TH + 6) * BL_SP];
-    __shared__ __align__(16) unsigned short sH[(BL_TH + 6) * BL_TW];
-    int l = 0;
-    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.geom[l + 1].blurTileBase) l++;
-    const LevelGeom g = P.geom[l];
-    const int b = blockIdx.y;
-    const int t = blockIdx.x - g.blurTileBase;
-    const int x0 = (t % g.blurTilesX) * BL_TW, y0 = (t / g.blurTilesX) * BL_TH;
-    int pitch, valid;
-    const uint8_t *src = level_ptr(P, g, l, b, pitch, valid);
-    uint8_t *dst = P.blur + (size_t)b * P.pyrStride + g.imgOff;
-    const int W = g.w, H = g.h;
-    // stage rows y0-3 .. y0+TH+2 (reflected), columns [x0-16, x0+TW+16) clipped to the row (reflected later)
-    const int xb = max(x0 - 16, 0);
-    const int xe = min(x0 + BL_TW + 16, (W + 15) & ~15);
-    const int nbytes = xe - xb;
-    const int rows = min(BL_TH, H - y0) + 6;
-    {
-        const bool vec = ((((size_t)src) | (size_t)pitch) & 15) == 0;
-        const int chunks = nbytes >> 4;
-        for (int i = threadIdx.x; i < rows * chunks; i += blockDim.x) {
-            const int r = i / chunks, c = i - r * chunks, x = xb + (c << 4);
-            const int sy = reflect101(y0 - 3 + r, H);
-            const uint8_t *p = src + (size_t)sy * pitch + x;
-            uint4 v;
-            if (vec && x + 16 <= valid) {
-                v = ldg_nc_v4(p);
-            } else {
-                unsigned int wd[4] = {0, 0, 0, 0};
-#pragma unroll
-                for (int k = 0; k < 16; k++)
-                    if (x + k < W) wd[k >> 2] |= (unsigned int)__ldg(p + k) << ((k & 3) * 8);
-                v = make_uint4(wd[0], wd[1], wd[2], wd[3]);
-            }
-            *reinterpret_cast<uint4 *>(sIn + r * BL_SP + (c << 4)) = v;
-        }
-    }
-    __syncthreads();
-    const int tw = min(BL_TW, W - x0);
-    // horizontal: every staged row, tw columns
-    for (int i = threadIdx.x; i < rows * BL_TW; i += blockDim.x) {
-        const int r = i / BL_TW, x = i - r * BL_TW;
-        if (x >= tw) continue;
-        const uint8_t *row = sIn + r * BL_SP - xb;
-        const int gx = x0 + x;
-        int acc;
-        if (gx >= 3 && gx < W - 3) {
-            acc = 18 * (row[gx - 3] + row[gx + 3]) + 34 * (row[gx - 2] + row[gx + 2]) +
-                  48 * (row[gx - 1] + row[gx + 1]) + 56 * row[gx];
-        } else {
-            acc = 18 * (row[reflect101(gx - 3, W)] + row[reflect101(gx + 3, W)]) +
-                  34 * (row[reflect101(gx - 2, W)] + row[reflect101(gx + 2, W)]) +
-                  48 * (row[reflect101(gx - 1, W)] + row[reflect101(gx + 1, W)]) + 56 * row[gx];
-        }
-        sH[r * BL_TW + x] = (unsigned short)acc;
-    }
-    __syncthreads();
-    // vertical: thread -> 4 adjacent columns, rows strided by 8
-    const int tx = (threadIdx.x & 31) * 4, ty = threadIdx.x >> 5;
-    if (tx < tw) {
-        for (int y = ty; y < rows - 6; y += 8) {
-            unsigned int packed = 0;
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const unsigned short *c = sH + y * BL_TW + tx + k;
-                unsigned int acc = 18u * (c[0] + c[6 * BL_TW]) + 34u * (c[BL_TW] + c[5 * BL_TW]) +
-                                   48u * (c[2 * BL_TW] + c[4 * BL_TW]) + 56u * c[3 * BL_TW];
-                packed |= ((acc + 32768u) >> 16) << (8 * k);
-            }
-            *reinterpret_cast<unsigned int *>(dst + (size_t)(y0 + y) * g.pitch + x0 + tx) = packed;
-        }
-    }
-}
-
+// E7 blur7: see blur_kernel.cuh
 // E3+E4 fast_cells: see fast_kernel.cuh
 
 #endif // ORBB200_EXTRACT_IMPL

@@ -7,6 +7,7 @@
 #include <new>
 
 #define ORBB200_EXTRACT_IMPL
+#include "blur_kernel.cuh"
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
 #include "fast_kernel.cuh"
