@@ -39,6 +39,11 @@ struct orbb200_extractor {
     int *d_stSad = nullptr, *d_stN = nullptr, *d_stRows = nullptr;
     size_t stElems = 0, stRowElems = 0;
     int stPairs = 0;
+    // host-API pipeline (orbb200_extract_batch): copy / D2H streams, double-buffered packed staging
+    cudaStream_t copyStream = nullptr, d2hStream = nullptr;
+    cudaEvent_t evH2D[2] = {nullptr, nullptr}, evDone[2] = {nullptr, nullptr};
+    uint8_t *d_stage[2] = {nullptr, nullptr};
+    size_t stageBytes = 0;
     // last call
     int lastBatch = 0, lastCap = 0;
     const uint8_t *lastL0 = nullptr;
@@ -58,6 +63,7 @@ struct orbb200_extractor {
 namespace orbb200 {
 int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch);
 int extractor_ensure_outputs(orbb200_extractor *e, int batch, int cap);
+int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes);
 int extractor_run(orbb200_extractor *e, const uint8_t *l0, size_t l0ImgStride, int l0Pitch, int l0Valid, int batch,
                   orbb200_keypoint *kps_d, uint8_t *desc_d, int cap, int *nOut_d);
 } // namespace orbb200

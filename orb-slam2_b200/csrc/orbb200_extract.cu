@@ -185,6 +185,26 @@ int extractor_ensure_outputs(orbb200_extractor *e, int batch, int cap)
     return ORBB200_OK;
 }
 
+int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes)
+{
+    if (!e->copyStream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
+    if (!e->d2hStream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&e->d2hStream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+        if (!e->evH2D[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evH2D[i], cudaEventDisableTiming));
+        if (!e->evDone[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evDone[i], cudaEventDisableTiming));
+    }
+    if (e->stageBytes < stageBytes) {
+        ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
+        ORB_CUDA_OK(cudaStreamSynchronize(e->copyStream));
+        for (int i = 0; i < 2; i++) {
+            if (e->d_stage[i]) { cudaFree(e->d_stage[i]); e->d_stage[i] = nullptr; }
+            ORB_CUDA_OK(cudaMalloc((void **)&e->d_stage[i], stageBytes + 256));
+        }
+        e->stageBytes = stageBytes;
+    }
+    return ORBB200_OK;
+}
+
 } // namespace orbb200
 
 #include "extractor_api.inc"
