@@ -139,6 +139,18 @@ int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt,
 int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets,
                                 const int *cand_idx, uint16_t *dist, int device);
 
+/* F3 + F2 + distances in one call: Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:261-279, 444-456) on the
+ * target keypoints tkp[nt] (the caller's mvKeysUn; grid = mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv,
+ * FRAME_GRID_COLS x FRAME_GRID_ROWS), then Frame::GetFeaturesInArea (:386-442) for every query window
+ * windows[nq][5] = {x, y, r, minLevel, maxLevel}, candidates in the reference's order (ix outer, iy inner, insertion
+ * order inside a cell), and the DescriptorDistance of every candidate to qdesc[q].  Outputs: CSR cand_offsets[nq+1],
+ * cand_idx[], dist[].  Returns ORBB200_ERR_CAPACITY with cand_offsets filled when cand_cap is too small.  This is the
+ * device side of SearchByProjection / Fuse / SearchBySim3 / SearchForInitialization (src/ORBmatcher.cc:48-136, 305-418,
+ * 430-563, 873-1164, 1166-1390, 1396-1682); the ordered accept / claim loop stays in the host facade. */
+int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int nt, float minX, float minY, float invW,
+                          float invH, int cols, int rows, const float *windows, const uint8_t *qdesc, int nq,
+                          int *cand_offsets, int *cand_idx, uint16_t *dist, int cand_cap, int device);
+
 /* merge of per-shard top-2 results (config 5, database sharded by rows; shard s's indices already global):
  * parts[s*nq + i]; ties on best_dist go to the lowest shard (= lowest global index, first-seen rule). */
 int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);

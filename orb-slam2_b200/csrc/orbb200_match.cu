@@ -6,6 +6,7 @@
 #include "extractor_host.cuh"
 #include "match_kernels.cuh"
 #include "stereo_kernel.cuh"
+#include "window_kernels.cuh"
 
 namespace orbb200 {
 
@@ -13,8 +14,8 @@ namespace orbb200 {
 struct Scratch {
     int device = -1;
     cudaStream_t stream = nullptr;
-    void *buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t cap[6] = {0, 0, 0, 0, 0, 0};
+    void *buf[12] = {};
+    size_t cap[12] = {};
 };
 static thread_local Scratch g_scratch;
 
@@ -24,7 +25,7 @@ static int scratch_bind(int device)
     ORB_CUDA_OK(cudaSetDevice(device));
     Scratch &s = g_scratch;
     if (s.device != device) {
-        for (int i = 0; i < 6; i++) { s.buf[i] = nullptr; s.cap[i] = 0; } // buffers of another device are leaked on purpose
+        for (int i = 0; i < 12; i++) { s.buf[i] = nullptr; s.cap[i] = 0; } // buffers of another device are leaked on purpose
         s.stream = nullptr;
         s.device = device;
     }
@@ -181,6 +182,57 @@ int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int 
     k_candidate_distances<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
                                                                (const int *)didx, (unsigned short *)dout);
     ORB_CUDA_OK(cudaMemcpyAsync(dist, dout, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int nt, float minX, float minY, float invW, float invH,
+                          int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets, int *cand_idx,
+                          uint16_t *dist, int cand_cap, int device)
+{
+    ORB_ARG_OK(cand_offsets != nullptr, "cand_offsets is null");
+    for (int i = 0; i <= std::max(nq, 0); i++) cand_offsets[i] = 0;
+    if (nq <= 0 || nt <= 0) return ORBB200_OK;
+    ORB_ARG_OK(tkp && tdesc && windows && qdesc && cols > 0 && rows > 0 && cols * rows <= 11000, "bad arguments");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    const int nc = cols * rows;
+    void *dkp, *dtd, *dwin, *dqd, *dcs, *dci, *dcnt;
+    if ((rc = scratch_get(0, (size_t)nq * 32, &dqd)) || (rc = scratch_get(1, (size_t)nt * 32, &dtd)) ||
+        (rc = scratch_get(6, (size_t)nt * sizeof(orbb200_keypoint), &dkp)) || (rc = scratch_get(7, (size_t)nq * 20, &dwin)) ||
+        (rc = scratch_get(8, (size_t)(nc + 1) * 4, &dcs)) || (rc = scratch_get(9, (size_t)nt * 4, &dci)) ||
+        (rc = scratch_get(3, (size_t)(nq + 1) * 4, &dcnt)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dtd, tdesc, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dwin, windows, (size_t)nq * 20, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dqd, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    WindowParams W;
+    memset(&W, 0, sizeof(W));
+    W.G.kp = (const orbb200_keypoint *)dkp; W.G.n = nt;
+    W.G.minX = minX; W.G.minY = minY; W.G.invW = invW; W.G.invH = invH; W.G.cols = cols; W.G.rows = rows;
+    W.G.cellStart = (int *)dcs; W.G.cellItems = (int *)dci;
+    W.win = (const float *)dwin; W.qdesc = (const uint8_t *)dqd; W.tdesc = (const uint8_t *)dtd; W.nq = nq;
+    W.counts = (int *)dcnt;
+    k_grid_build<<<1, 256, (size_t)(nc + 1) * 4, st>>>(W.G);
+    k_window_count<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
+    k_scan_counts<<<1, 1024, 0, st>>>((int *)dcnt, nq);
+    ORB_CUDA_OK(cudaMemcpyAsync(cand_offsets, dcnt, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    const int total = cand_offsets[nq];
+    if (total > cand_cap) {
+        set_error("orbb200_window_search: %d candidates, capacity is %d", total, cand_cap);
+        return ORBB200_ERR_CAPACITY; // cand_offsets is valid: the caller can size the buffers and call again
+    }
+    if (total == 0) return ORBB200_OK;
+    ORB_ARG_OK(cand_idx && dist, "null output");
+    void *dcand, *ddist;
+    if ((rc = scratch_get(4, (size_t)total * 4, &dcand)) || (rc = scratch_get(2, (size_t)total * 2, &ddist))) return rc;
+    W.candIdx = (int *)dcand; W.dist = (unsigned short *)ddist; W.cap = total;
+    k_window_fill<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
+    ORB_CUDA_OK(cudaMemcpyAsync(cand_idx, dcand, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dist, ddist, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_OK(cudaStreamSynchronize(st));
     return ORBB200_OK;
 }

@@ -22,7 +22,7 @@ EXPORTS = [
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
-    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_merge_top2",
+    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_window_search", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
     "orbb200_stereo_match_batch_device", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
 ]
@@ -69,6 +69,7 @@ def lib():
     L.orbb200_match_bruteforce_top2_device.argtypes = [vp, ip, vp, ip, vp, ip, vp]
     L.orbb200_match_candidates.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
     L.orbb200_candidate_distances.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
+    L.orbb200_window_search.argtypes = [vp, vp, ip, fp, fp, fp, fp, ip, ip, vp, vp, ip, vp, vp, vp, ip, ip]
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
@@ -273,6 +274,28 @@ class ORBmatcher:
         out = np.zeros(max(int(offsets[-1]), 1), np.uint16)
         check(self.L.orbb200_candidate_distances(_p(q), len(q), _p(t), len(t), _p(offsets), _p(idx), _p(out), self.device))
         return out[:int(offsets[-1])]
+
+    def window_search(self, tkps, tdesc, grid, windows, qdesc, cap=None):
+        """F3 + F2 + distances (orbb200_window_search).  grid = (minX, minY, invW, invH, cols, rows);
+        windows [nq,5] float32 = x, y, r, minLevel, maxLevel.  Returns (offsets[nq+1], cand_idx, dist)."""
+        tkps = np.ascontiguousarray(tkps, KP_DTYPE)
+        tdesc = np.ascontiguousarray(tdesc, np.uint8)
+        windows = np.ascontiguousarray(windows, np.float32)
+        qdesc = np.ascontiguousarray(qdesc, np.uint8)
+        nq = len(windows)
+        offs = np.zeros(nq + 1, np.int32)
+        cap = cap if cap is not None else max(64 * nq, 1)
+        minX, minY, invW, invH, cols, rows = grid
+        while True:
+            idx = np.zeros(max(cap, 1), np.int32)
+            dist = np.zeros(max(cap, 1), np.uint16)
+            rc = self.L.orbb200_window_search(_p(tkps), _p(tdesc), len(tkps), minX, minY, invW, invH, cols, rows, _p(windows),
+                                              _p(qdesc), nq, _p(offs), _p(idx), _p(dist), cap, self.device)
+            if rc == -3 and offs[-1] > cap:  # ORBB200_ERR_CAPACITY: offsets are valid, retry with the exact size
+                cap = int(offs[-1])
+                continue
+            check(rc)
+            return offs, idx[:offs[-1]], dist[:offs[-1]]
 
     def merge_top2(self, parts):
         parts = np.ascontiguousarray(parts, TOP2_DTYPE)

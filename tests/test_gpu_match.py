@@ -125,3 +125,41 @@ def test_stereo_match_batch_equals_single(configs):
         nL = len(kL)
         assert nL == n[2 * p] and snv == nv[p] and snv > 200
         assert np.array_equal(uR[p, :nL], suR[:nL]) and np.array_equal(depth[p, :nL], sdepth[:nL])
+
+
+def test_window_search_equals_oracle_grid_and_area(configs):
+    """F3 (AssignFeaturesToGrid) + F2 (GetFeaturesInArea) + distances on the device == the oracle's restatement of
+    src/Frame.cc:261-279, 386-442: same candidates in the same order for every window, same distances."""
+    w, h, nf, sfac, nl, ini, mn = configs["tum"]
+    img = synth.textured_frame(w, h, 4242)
+    kps, desc = orbb200.ORBextractor(nf, sfac, nl, ini, mn)(img)
+    rng = np.random.default_rng(17)
+    minX, minY, maxX, maxY = 0.0, 0.0, float(w), float(h)
+    cols, rows = 64, 48
+    invW, invH = np.float32(cols) / np.float32(maxX - minX), np.float32(rows) / np.float32(maxY - minY)
+    nq = 700
+    src = rng.integers(0, len(kps), nq)
+    win = np.zeros((nq, 5), np.float32)
+    win[:, 0] = kps["x"][src] + rng.normal(0, 3, nq)
+    win[:, 1] = kps["y"][src] + rng.normal(0, 3, nq)
+    win[:, 2] = rng.choice([2.5, 4.0, 15.0, 40.0, 100.0], nq) * rng.choice([1.0, 1.2, 1.44], nq)
+    lev = kps["octave"][src]
+    win[:, 3] = np.where(rng.random(nq) < 0.3, -1, lev - 1)
+    win[:, 4] = np.where(win[:, 3] < 0, np.where(rng.random(nq) < 0.5, -1, lev), lev)
+    win[0, :2] = (-500, -500)        # window entirely outside the grid
+    win[1, :3] = (5, 5, 30)          # clipped at the image corner
+    win[2, :3] = (w - 2, h - 2, 50)
+    qdesc = desc[src].copy()
+    qdesc ^= rng.integers(0, 256, qdesc.shape, dtype=np.uint8) & rng.integers(0, 256, qdesc.shape, dtype=np.uint8) & 0x11
+    offs, idx, dist = orbb200.ORBmatcher().window_search(kps, desc, (minX, minY, float(invW), float(invH), cols, rows), win, qdesc, cap=100)
+    start, items = ref_cpu.assign_grid(kps, minX, minY, invW, invH, cols, rows)
+    total = 0
+    for q in range(nq):
+        ref = ref_cpu.features_in_area(kps, start, items, minX, minY, invW, invH, win[q, 0], win[q, 1], win[q, 2],
+                                       int(win[q, 3]), int(win[q, 4]), cols, rows)
+        got = idx[offs[q]:offs[q + 1]]
+        assert np.array_equal(got, ref), (q, got[:10], ref[:10])
+        d = np.unpackbits(desc[ref] ^ qdesc[q], axis=1).sum(axis=1) if len(ref) else np.zeros(0)
+        assert np.array_equal(dist[offs[q]:offs[q + 1]], d), q
+        total += len(ref)
+    assert offs[0] == 0 and offs[-1] == total and total > 5000 and offs[1] == 0
