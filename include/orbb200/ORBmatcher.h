@@ -56,7 +56,7 @@ public:
         // prologue: queries in reference order with their windows
         std::vector<int> qMP;                 // index into vpMapPoints
         std::vector<float> qR;                // r * scale[level]
-        std::vector<int> offs(1, 0), cand;
+        std::vector<float> windows;           // F.GetFeaturesInArea arguments (:77-78), evaluated on the device
         std::vector<unsigned char> qDesc;
         for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++) {
             MapPointT *pMP = vpMapPoints[iMP];
@@ -66,17 +66,16 @@ public:
             float r = RadiusByViewingCos(pMP->mTrackViewCos);
             if (bFactor) r *= th;
             const float win = r * F.mvScaleFactors[nPredictedLevel];
-            const std::vector<size_t> vIndices = F.GetFeaturesInArea(pMP->mTrackProjX, pMP->mTrackProjY, win, nPredictedLevel - 1, nPredictedLevel);
-            if (vIndices.empty()) continue;
             qMP.push_back((int)iMP);
             qR.push_back(win);
-            for (size_t k = 0; k < vIndices.size(); k++) cand.push_back((int)vIndices[k]);
-            offs.push_back((int)cand.size());
+            const float wq[5] = {pMP->mTrackProjX, pMP->mTrackProjY, win, (float)(nPredictedLevel - 1), (float)nPredictedLevel};
+            windows.insert(windows.end(), wq, wq + 5);
             const cv::Mat d = pMP->GetDescriptor();
             qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
         }
+        std::vector<int> offs, cand;
         std::vector<uint16_t> dist;
-        if (!distances(qDesc, (int)qMP.size(), F.mDescriptors, offs, cand, dist)) return 0;
+        if (!window_search_frame(F, windows, qDesc, offs, cand, dist)) return 0;
         // epilogue: the reference loop (:86-131) on precomputed distances
         int nmatches = 0;
         for (size_t q = 0; q < qMP.size(); q++) {
@@ -186,6 +185,102 @@ public:
         return nmatches;
     }
 
+    // Motion-model tracking (src/ORBmatcher.cc:1396-1553; callers src/Tracking.cc:1065, 1072).
+    template <class FrameT>
+    int SearchByProjection(FrameT &CurrentFrame, const FrameT &LastFrame, const float th, const bool bMono)
+    {
+        typedef typename std::remove_pointer<typename std::remove_reference<decltype(LastFrame.mvpMapPoints[0])>::type>::type MapPointT;
+        int nmatches = 0;
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        float Rcw[9], tcw[3], Rlw[9], tlw[3];
+        pose_Rt(CurrentFrame.mTcw, Rcw, tcw);
+        pose_Rt(LastFrame.mTcw, Rlw, tlw);
+        // twc = -Rcw^T * tcw ; tlc = Rlw * twc + tlw  (cv::gemm accumulates 32F products in double)
+        float twc[3], tlc[3];
+        for (int i = 0; i < 3; i++) twc[i] = -(float)((double)Rcw[i] * tcw[0] + (double)Rcw[3 + i] * tcw[1] + (double)Rcw[6 + i] * tcw[2]);
+        mat_Rx_t(Rlw, twc, tlw, tlc);
+        const bool bForward = tlc[2] > CurrentFrame.mb && !bMono;
+        const bool bBackward = -tlc[2] > CurrentFrame.mb && !bMono;
+        // prologue: projections and windows, in LastFrame index order (:1419-1472)
+        std::vector<int> qI;
+        std::vector<float> win, qU, qInvz, qRadius;
+        std::vector<unsigned char> qDesc;
+        for (int i = 0; i < LastFrame.N; i++) {
+            MapPointT *pMP = LastFrame.mvpMapPoints[i];
+            if (!pMP) continue;
+            if (LastFrame.mvbOutlier[i]) continue;
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+            const float xw[3] = {x3Dw.template at<float>(0, 0), x3Dw.template at<float>(1, 0), x3Dw.template at<float>(2, 0)};
+            float x3Dc[3];
+            mat_Rx_t(Rcw, xw, tcw, x3Dc);
+            const float xc = x3Dc[0], yc = x3Dc[1];
+            const float invzc = 1.0 / x3Dc[2];
+            if (invzc < 0) continue;
+            const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+            const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+            if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+            if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+            const int nLastOctave = LastFrame.mvKeys[i].octave;
+            const float radius = th * CurrentFrame.mvScaleFactors[nLastOctave];
+            int minL, maxL;
+            if (bForward) { minL = nLastOctave; maxL = -1; }
+            else if (bBackward) { minL = 0; maxL = nLastOctave; }
+            else { minL = nLastOctave - 1; maxL = nLastOctave + 1; }
+            qI.push_back(i); qU.push_back(u); qInvz.push_back(invzc); qRadius.push_back(radius);
+            const float wq[5] = {u, v, radius, (float)minL, (float)maxL};
+            win.insert(win.end(), wq, wq + 5);
+            const cv::Mat d = pMP->GetDescriptor();
+            qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_frame(CurrentFrame, win, qDesc, offs, cand, dist)) return 0;
+        // epilogue (:1474-1527)
+        for (size_t q = 0; q < qI.size(); q++) {
+            if (offs[q] == offs[q + 1]) continue;
+            const int i = qI[q];
+            MapPointT *pMP = LastFrame.mvpMapPoints[i];
+            int bestDist = 256, bestIdx2 = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t i2 = (size_t)cand[c];
+                if (CurrentFrame.mvpMapPoints[i2])
+                    if (CurrentFrame.mvpMapPoints[i2]->Observations() > 0) continue;
+                if (CurrentFrame.mvuRight[i2] > 0) {
+                    const float ur = qU[q] - CurrentFrame.mbf * qInvz[q];
+                    const float er = std::fabs(ur - CurrentFrame.mvuRight[i2]);
+                    if (er > qRadius[q]) continue;
+                }
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx2 = (int)i2; }
+            }
+            if (bestDist <= TH_HIGH) {
+                CurrentFrame.mvpMapPoints[bestIdx2] = pMP;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = LastFrame.mvKeysUn[i].angle - CurrentFrame.mvKeysUn[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2);
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i != ind1 && i != ind2 && i != ind3) {
+                    for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                        CurrentFrame.mvpMapPoints[rotHist[i][j]] = static_cast<MapPointT *>(NULL);
+                        nmatches--;
+                    }
+                }
+            }
+        }
+        return nmatches;
+    }
+
     void SetDevice(int device) { device_ = device; } /* extension: GPU used by the searches (default: current) */
 
 public:
@@ -212,6 +307,69 @@ protected:
             return false;
         }
         return true;
+    }
+
+    // R (row-major 3x3) and t of a 4x4 CV_32F pose, like Tcw.rowRange(0,3).colRange(0,3) / .col(3)
+    static void pose_Rt(const cv::Mat &T, float *R, float *t)
+    {
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) R[3 * r + c] = T.at<float>(r, c);
+            t[r] = T.at<float>(r, 3);
+        }
+    }
+    // y = R*x + t as cv::gemm evaluates it for CV_32F operands: products and the added term accumulate in double
+    static void mat_Rx_t(const float *R, const float *x, const float *t, float *y)
+    {
+        for (int r = 0; r < 3; r++)
+            y[r] = (float)((double)R[3 * r] * x[0] + (double)R[3 * r + 1] * x[1] + (double)R[3 * r + 2] * x[2] + (double)t[r]);
+    }
+
+    // Frame::GetFeaturesInArea for every window of a search + all candidate distances, in ONE device call
+    // (orbb200_window_search: the frame's 64x48 grid is rebuilt on the device from mvKeysUn, so the caller's
+    // Frame::mGrid is not read).  windows: 5 floats per query = x, y, r, minLevel, maxLevel.
+    template <class FrameT>
+    bool window_search_frame(const FrameT &F, const std::vector<float> &windows, const std::vector<unsigned char> &qDesc,
+                             std::vector<int> &offs, std::vector<int> &cand, std::vector<uint16_t> &dist)
+    {
+#ifdef FRAME_GRID_COLS
+        const int cols = FRAME_GRID_COLS, rows = FRAME_GRID_ROWS;
+#else
+        const int cols = 64, rows = 48;
+#endif
+        return window_search(F.mvKeysUn, F.mDescriptors, F.mnMinX, F.mnMinY, F.mfGridElementWidthInv, F.mfGridElementHeightInv,
+                             cols, rows, windows, qDesc, offs, cand, dist);
+    }
+
+    bool window_search(const std::vector<cv::KeyPoint> &tkps, const cv::Mat &targets, float minX, float minY, float invW, float invH,
+                       int cols, int rows, const std::vector<float> &windows, const std::vector<unsigned char> &qDesc,
+                       std::vector<int> &offs, std::vector<int> &cand, std::vector<uint16_t> &dist)
+    {
+        const int nq = (int)(windows.size() / 5);
+        offs.assign(nq + 1, 0);
+        cand.assign(1, 0);
+        dist.assign(1, 0);
+        if (nq == 0 || tkps.empty()) return true;
+        const unsigned char *t = targets.ptr();
+        std::vector<unsigned char> packed;
+        if (!targets.isContinuous()) {
+            packed.resize((size_t)targets.rows * 32);
+            for (int r = 0; r < targets.rows; r++) std::memcpy(&packed[(size_t)r * 32], targets.ptr(r), 32);
+            t = packed.data();
+        }
+        int cap = nq * 48 + 64;
+        for (int attempt = 0; attempt < 2; attempt++) {
+            cand.assign(cap, 0);
+            dist.assign(cap, 0);
+            const int rc = orbb200_window_search(reinterpret_cast<const orbb200_keypoint *>(tkps.data()), t, (int)tkps.size(), minX, minY,
+                                                 invW, invH, cols, rows, windows.data(), qDesc.data(), nq, offs.data(), cand.data(),
+                                                 dist.data(), cap, device_);
+            if (rc == ORBB200_OK) return true;
+            if (rc == ORBB200_ERR_CAPACITY && offs[nq] > cap) { cap = offs[nq]; continue; } // offsets are valid: exact size
+            break;
+        }
+        std::cerr << "ORBmatcher (orbb200): " << orbb200_last_error() << std::endl; // no CPU fallback: 0 matches
+        offs.assign(nq + 1, 0);
+        return false;
     }
 
     // src/ORBmatcher.cc:147-164

@@ -11,7 +11,11 @@
 
 #include "orbb200/ORBmatcher.h"
 
-extern "C" int ref_descriptor_distance(const unsigned char *a, const unsigned char *b); // oracle/orb_ref.c
+// oracle/orb_ref.c (checker only)
+extern "C" int ref_descriptor_distance(const unsigned char *a, const unsigned char *b);
+extern "C" void ref_assign_grid(const void *kp, int n, float minX, float minY, float invW, float invH, int cols, int rows, int *cell_start, int *cell_items);
+extern "C" int ref_features_in_area(const void *kp, const int *cell_start, const int *cell_items, float minX, float minY, float invW, float invH,
+                                    int cols, int rows, float x, float y, float r, int minLevel, int maxLevel, int *out, int cap);
 
 static unsigned long long g_s = 88172645463325252ull;
 static unsigned rnd() { g_s ^= g_s << 13; g_s ^= g_s >> 7; g_s ^= g_s << 17; return (unsigned)(g_s >> 11); }
@@ -21,10 +25,11 @@ struct MapPoint {
     bool mbTrackInView = true, bad = false;
     int mnTrackScaleLevel = 0, obs = 1;
     float mTrackViewCos = 1.f, mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0;
-    cv::Mat desc;
+    cv::Mat desc, pos;
     bool isBad() { return bad; }
     int Observations() { return obs; }
     cv::Mat GetDescriptor() { return desc.clone(); }
+    cv::Mat GetWorldPos() { return pos.clone(); }
 };
 
 struct Frame {
@@ -32,22 +37,25 @@ struct Frame {
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
     std::vector<float> mvuRight, mvScaleFactors;
     std::vector<MapPoint *> mvpMapPoints;
-    cv::Mat mDescriptors;
+    std::vector<bool> mvbOutlier;
+    cv::Mat mDescriptors, mTcw;
+    float mb = 0.5372f, mbf = 386.1448f, fx = 718.856f, fy = 718.856f, cx = 320.f, cy = 240.f;
+    float mnMinX = 0, mnMinY = 0, mnMaxX = 640, mnMaxY = 480, mfGridElementWidthInv = 64.f / 640.f, mfGridElementHeightInv = 48.f / 480.f;
     std::map<unsigned int, std::vector<unsigned int>> mFeatVec; // DBoW2::FeatureVector is a std::map of index lists
-    // stand-in of Frame::GetFeaturesInArea (src/Frame.cc:386-442): index order, square window, level band
-    std::vector<size_t> GetFeaturesInArea(const float &x, const float &y, const float &r, const int minLevel, const int maxLevel) const
+    // Frame::AssignFeaturesToGrid + GetFeaturesInArea (src/Frame.cc:261-279, 386-442) through the CPU oracle
+    mutable std::vector<int> cellStart, cellItems;
+    std::vector<size_t> GetFeaturesInArea(const float &x, const float &y, const float &r, const int minLevel = -1, const int maxLevel = -1) const
     {
-        std::vector<size_t> v;
-        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
-        for (int i = 0; i < N; i++) {
-            const cv::KeyPoint &kp = mvKeysUn[i];
-            if (bCheckLevels) {
-                if (kp.octave < minLevel) continue;
-                if (maxLevel >= 0 && kp.octave > maxLevel) continue;
-            }
-            if (std::fabs(kp.pt.x - x) < r && std::fabs(kp.pt.y - y) < r) v.push_back(i);
+        static_assert(sizeof(cv::KeyPoint) == 28, "layout");
+        if (cellStart.empty()) {
+            cellStart.assign(64 * 48 + 1, 0);
+            cellItems.assign(N > 0 ? N : 1, 0);
+            ref_assign_grid(mvKeysUn.data(), N, mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv, 64, 48, cellStart.data(), cellItems.data());
         }
-        return v;
+        std::vector<int> out(N > 0 ? N : 1);
+        const int n = ref_features_in_area(mvKeysUn.data(), cellStart.data(), cellItems.data(), mnMinX, mnMinY, mfGridElementWidthInv,
+                                           mfGridElementHeightInv, 64, 48, x, y, r, minLevel, maxLevel, out.data(), (int)out.size());
+        return std::vector<size_t>(out.begin(), out.begin() + n);
     }
 };
 
@@ -62,7 +70,7 @@ struct KeyFrame {
 static void fill_frame(Frame &F, int N)
 {
     F.N = N;
-    F.mvKeys.resize(N); F.mvuRight.assign(N, -1.f); F.mvpMapPoints.assign(N, nullptr);
+    F.mvKeys.resize(N); F.mvuRight.assign(N, -1.f); F.mvpMapPoints.assign(N, nullptr); F.mvbOutlier.assign(N, false);
     F.mDescriptors.create(N, 32, CV_8U);
     F.mvScaleFactors.resize(8);
     F.mvScaleFactors[0] = 1.f;
@@ -151,6 +159,118 @@ int main()
         for (int i = 0; i < F1.N; i++) same = same && F1.mvpMapPoints[i] == F2.mvpMapPoints[i];
         printf("%s SearchByProjection(local map): %d matches (reference loop %d)\n", same && ng > 300 ? "ok" : "FAIL", ng, nr);
         fails += !(same && ng > 300);
+    }
+    // ---- M3: SearchByProjection(CurrentFrame, LastFrame, th, bMono)
+    for (int variant = 0; variant < 3; variant++) {
+        Frame Last, Cur1, Cur2;
+        fill_frame(Last, 1300);
+        fill_frame(Cur1, 1500);
+        // poses: last = identity, current = small rotation about y + translation (variant 1: forward, 2: backward motion)
+        Last.mTcw.create(4, 4, CV_32F); Cur1.mTcw.create(4, 4, CV_32F);
+        for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) { Last.mTcw.at<float>(r, c) = r == c; Cur1.mTcw.at<float>(r, c) = r == c; }
+        const float ang = 0.01f;
+        Cur1.mTcw.at<float>(0, 0) = std::cos(ang); Cur1.mTcw.at<float>(0, 2) = std::sin(ang);
+        Cur1.mTcw.at<float>(2, 0) = -std::sin(ang); Cur1.mTcw.at<float>(2, 2) = std::cos(ang);
+        Cur1.mTcw.at<float>(0, 3) = 0.05f; Cur1.mTcw.at<float>(2, 3) = variant == 1 ? -1.0f : (variant == 2 ? 1.0f : 0.1f);
+        std::vector<MapPoint> store(Last.N);
+        for (int i = 0; i < Last.N; i++) {
+            MapPoint &m = store[i];
+            // back-project the last keypoint at a random depth, place a matching feature near its projection in Cur
+            const float z = 4.f + 30.f * rndf();
+            m.pos.create(3, 1, CV_32F);
+            m.pos.at<float>(0, 0) = (Last.mvKeys[i].pt.x - Last.cx) * z / Last.fx;
+            m.pos.at<float>(1, 0) = (Last.mvKeys[i].pt.y - Last.cy) * z / Last.fy;
+            m.pos.at<float>(2, 0) = z;
+            m.desc.create(1, 32, CV_8U);
+            memcpy(m.desc.ptr(), Last.mDescriptors.ptr(i), 32);
+            m.obs = rnd() % 5 == 0 ? 0 : 3;
+            if (rnd() % 8) Last.mvpMapPoints[i] = &m;
+            Last.mvbOutlier[i] = rnd() % 12 == 0;
+            // projection in the current frame
+            const float *T = Cur1.mTcw.ptr<float>();
+            const float xc = T[0] * m.pos.at<float>(0, 0) + T[1] * m.pos.at<float>(1, 0) + T[2] * z + T[3];
+            const float yc = T[4] * m.pos.at<float>(0, 0) + T[5] * m.pos.at<float>(1, 0) + T[6] * z + T[7];
+            const float zc = T[8] * m.pos.at<float>(0, 0) + T[9] * m.pos.at<float>(1, 0) + T[10] * z + T[11];
+            const int j = i % Cur1.N;
+            if (zc > 0.1f && rnd() % 4) {
+                Cur1.mvKeys[j].pt.x = Cur1.fx * xc / zc + Cur1.cx + (rndf() - 0.5f) * 6;
+                Cur1.mvKeys[j].pt.y = Cur1.fy * yc / zc + Cur1.cy + (rndf() - 0.5f) * 6;
+                Cur1.mvKeys[j].octave = std::max(0, std::min(7, Last.mvKeys[i].octave + (int)(rnd() % 3) - 1));
+                Cur1.mvKeys[j].angle = std::fmod(Last.mvKeys[i].angle + (rnd() % 8 ? 5.f : 170.f * rndf()), 360.f);
+                noisy_copy(Last.mDescriptors.ptr(i), Cur1.mDescriptors.ptr(j), rnd() % 80);
+                if (Cur1.mvuRight[j] > 0) Cur1.mvuRight[j] = Cur1.mvKeys[j].pt.x - Cur1.mbf / zc + (rndf() - 0.5f) * 10;
+            }
+        }
+        Cur1.mvKeysUn = Cur1.mvKeys;
+        Cur2 = Cur1;
+        Cur2.mDescriptors = Cur1.mDescriptors.clone();
+        ORB_SLAM2::ORBmatcher matcher(0.9f, true);
+        const int ng = matcher.SearchByProjection(Cur1, Last, 15.f, false);
+        // reference loop (src/ORBmatcher.cc:1396-1553) with the oracle's distance and grid
+        int nr = 0;
+        {
+            Frame &C = Cur2;
+            std::vector<int> rotHist[30];
+            const float *Tc = C.mTcw.ptr<float>(), *Tl = Last.mTcw.ptr<float>();
+            float twc[3], tlc[3];
+            for (int i = 0; i < 3; i++) twc[i] = -(float)((double)Tc[i] * Tc[3] + (double)Tc[4 + i] * Tc[7] + (double)Tc[8 + i] * Tc[11]);
+            for (int r = 0; r < 3; r++) tlc[r] = (float)((double)Tl[4 * r] * twc[0] + (double)Tl[4 * r + 1] * twc[1] + (double)Tl[4 * r + 2] * twc[2] + (double)Tl[4 * r + 3]);
+            const bool bForward = tlc[2] > C.mb, bBackward = -tlc[2] > C.mb;
+            for (int i = 0; i < Last.N; i++) {
+                MapPoint *pMP = Last.mvpMapPoints[i];
+                if (!pMP || Last.mvbOutlier[i]) continue;
+                const float X = pMP->pos.at<float>(0, 0), Y = pMP->pos.at<float>(1, 0), Z = pMP->pos.at<float>(2, 0);
+                const float xc = (float)((double)Tc[0] * X + (double)Tc[1] * Y + (double)Tc[2] * Z + (double)Tc[3]);
+                const float yc = (float)((double)Tc[4] * X + (double)Tc[5] * Y + (double)Tc[6] * Z + (double)Tc[7]);
+                const float zc = (float)((double)Tc[8] * X + (double)Tc[9] * Y + (double)Tc[10] * Z + (double)Tc[11]);
+                const float invzc = 1.0 / zc;
+                if (invzc < 0) continue;
+                const float u = C.fx * xc * invzc + C.cx, v = C.fy * yc * invzc + C.cy;
+                if (u < C.mnMinX || u > C.mnMaxX || v < C.mnMinY || v > C.mnMaxY) continue;
+                const int oct = Last.mvKeys[i].octave;
+                const float radius = 15.f * C.mvScaleFactors[oct];
+                std::vector<size_t> vi;
+                if (bForward) vi = C.GetFeaturesInArea(u, v, radius, oct);
+                else if (bBackward) vi = C.GetFeaturesInArea(u, v, radius, 0, oct);
+                else vi = C.GetFeaturesInArea(u, v, radius, oct - 1, oct + 1);
+                if (vi.empty()) continue;
+                int bestDist = 256, bestIdx2 = -1;
+                for (size_t i2 : vi) {
+                    if (C.mvpMapPoints[i2] && C.mvpMapPoints[i2]->Observations() > 0) continue;
+                    if (C.mvuRight[i2] > 0) {
+                        const float ur = u - C.mbf * invzc;
+                        if (std::fabs(ur - C.mvuRight[i2]) > radius) continue;
+                    }
+                    const int d = ref_descriptor_distance(pMP->desc.ptr(), C.mDescriptors.ptr((int)i2));
+                    if (d < bestDist) { bestDist = d; bestIdx2 = (int)i2; }
+                }
+                if (bestDist <= 100) {
+                    C.mvpMapPoints[bestIdx2] = pMP;
+                    nr++;
+                    float rot = Last.mvKeysUn[i].angle - C.mvKeysUn[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * (1.0f / 30));
+                    if (bin == 30) bin = 0;
+                    rotHist[bin].push_back(bestIdx2);
+                }
+            }
+            int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                const int sz = (int)rotHist[i].size();
+                if (sz > m1) { m3 = m2; m2 = m1; m1 = sz; i3 = i2; i2 = i1; i1 = i; }
+                else if (sz > m2) { m3 = m2; m2 = sz; i3 = i2; i2 = i; }
+                else if (sz > m3) { m3 = sz; i3 = i; }
+            }
+            if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; } else if (m3 < 0.1f * (float)m1) i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                if (i == i1 || i == i2 || i == i3) continue;
+                for (int j : rotHist[i]) { C.mvpMapPoints[j] = nullptr; nr--; }
+            }
+        }
+        bool same = ng == nr;
+        for (int i = 0; i < Cur1.N; i++) same = same && Cur1.mvpMapPoints[i] == Cur2.mvpMapPoints[i];
+        printf("%s SearchByProjection(last frame, variant %d): %d matches (reference loop %d)\n", same && ng > 150 ? "ok" : "FAIL", variant, ng, nr);
+        fails += !(same && ng > 150);
     }
     // ---- M6: SearchByBoW(KeyFrame, Frame)
     {
