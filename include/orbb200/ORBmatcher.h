@@ -12,9 +12,11 @@
  *
  * The Search* members are templates over the caller's Frame / KeyFrame / MapPoint types: included in the reference
  * tree they bind to ORB_SLAM2::Frame etc. (same member names: mvKeysUn, mDescriptors, mvpMapPoints, mFeatVec, ...),
- * and this repo's tests bind them to small stand-ins (tests/cpp/facade_match.cpp).  Methods not listed here
- * (SearchForInitialization, SearchBySim3, Fuse, the other SearchByProjection overloads) follow the same three steps
- * over orbb200_candidate_distances / orbb200_match_candidates; see INTEGRATION.md 4.
+ * and this repo's tests bind them to small stand-ins (tests/cpp/facade_match.cpp).  The windowed searches send
+ * their windows to orbb200_window_search (grid build + GetFeaturesInArea + distances on the device); the BoW-node
+ * searches send CSR lists to orbb200_candidate_distances.  Not yet in this header: the Sim3 / relocalisation
+ * overloads (SearchByProjection(KF, Scw, ...), SearchByProjection(F, KF, sFound, ...), SearchBySim3, Fuse): they are
+ * the same prologue / device call / epilogue over a KeyFrame grid; see INTEGRATION.md 4.
  */
 #ifndef ORBB200_ORBMATCHER_H
 #define ORBB200_ORBMATCHER_H
@@ -24,6 +26,7 @@
 #include <cstring>
 #include <iostream>
 #include <type_traits>
+#include <utility>
 #include <vector>
 
 #ifdef ORBB200_USE_OPENCV
@@ -281,12 +284,195 @@ public:
         return nmatches;
     }
 
+    // Monocular map initialisation (src/ORBmatcher.cc:430-563; caller src/Tracking.cc:679).
+    template <class FrameT>
+    int SearchForInitialization(FrameT &F1, FrameT &F2, std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
+                                int windowSize = 10)
+    {
+        int nmatches = 0;
+        vnMatches12 = std::vector<int>(F1.mvKeysUn.size(), -1);
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        std::vector<int> vMatchedDistance(F2.mvKeysUn.size(), INT_MAX_);
+        std::vector<int> vnMatches21(F2.mvKeysUn.size(), -1);
+        // prologue: one window per level-0 keypoint of F1 (:446-458)
+        std::vector<int> qI1;
+        std::vector<float> windows;
+        std::vector<unsigned char> qDesc;
+        for (size_t i1 = 0, iend1 = F1.mvKeysUn.size(); i1 < iend1; i1++) {
+            const int level1 = F1.mvKeysUn[i1].octave;
+            if (level1 > 0) continue;
+            qI1.push_back((int)i1);
+            const float wq[5] = {vbPrevMatched[i1].x, vbPrevMatched[i1].y, (float)windowSize, (float)level1, (float)level1};
+            windows.insert(windows.end(), wq, wq + 5);
+            const unsigned char *d = F1.mDescriptors.ptr((int)i1);
+            qDesc.insert(qDesc.end(), d, d + 32);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_frame(F2, windows, qDesc, offs, cand, dist)) return 0;
+        // epilogue (:460-514): order dependent through vMatchedDistance / vnMatches21
+        for (size_t q = 0; q < qI1.size(); q++) {
+            if (offs[q] == offs[q + 1]) continue;
+            const int i1 = qI1[q];
+            int bestDist = INT_MAX_, bestDist2 = INT_MAX_, bestIdx2 = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const int i2 = cand[c];
+                const int d = dist[c];
+                if (vMatchedDistance[i2] <= d) continue;
+                if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = i2; }
+                else if (d < bestDist2) bestDist2 = d;
+            }
+            if (bestDist <= TH_LOW) {
+                if (bestDist < (float)bestDist2 * mfNNratio) {
+                    if (vnMatches21[bestIdx2] >= 0) {
+                        vnMatches12[vnMatches21[bestIdx2]] = -1;
+                        nmatches--;
+                    }
+                    vnMatches12[i1] = bestIdx2;
+                    vnMatches21[bestIdx2] = i1;
+                    vMatchedDistance[bestIdx2] = bestDist;
+                    nmatches++;
+                    if (mbCheckOrientation) {
+                        float rot = F1.mvKeysUn[i1].angle - F2.mvKeysUn[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back(i1);
+                    }
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i == ind1 || i == ind2 || i == ind3) continue;
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    const int idx1 = rotHist[i][j];
+                    if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+                }
+            }
+        }
+        for (size_t i1 = 0, iend1 = vnMatches12.size(); i1 < iend1; i1++)
+            if (vnMatches12[i1] >= 0) vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt;
+        return nmatches;
+    }
+
+    // Triangulation candidates between two keyframes (src/ORBmatcher.cc:704-871; caller src/LocalMapping.cc:309).
+    template <class KeyFrameT>
+    int SearchForTriangulation(KeyFrameT *pKF1, KeyFrameT *pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> > &vMatchedPairs,
+                               const bool bOnlyStereo)
+    {
+        // epipole of camera 1 in image 2 (:714-721)
+        const cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+        float R[9], c1[3], t2[3], C2[3];
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) R[3 * r + c] = R2w.template at<float>(r, c);
+            c1[r] = Cw.template at<float>(r, 0);
+            t2[r] = t2w.template at<float>(r, 0);
+        }
+        mat_Rx_t(R, c1, t2, C2);
+        const float invz = 1.0f / C2[2];
+        const float ex = pKF2->fx * C2[0] * invz + pKF2->cx;
+        const float ey = pKF2->fy * C2[1] * invz + pKF2->cy;
+        int nmatches = 0;
+        std::vector<int> vMatches12(pKF1->N, -1);
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        // prologue: BoW-node merge walk (:737-842); the per-candidate gates that do not depend on the distance
+        // (existing map point, stereo flag; vbMatched2 is never set in this code base) are applied here
+        std::vector<int> qIdx1, offs(1, 0), cand;
+        std::vector<unsigned char> qDesc;
+        typename std::remove_reference<decltype(pKF1->mFeatVec)>::type::const_iterator f1it = pKF1->mFeatVec.begin(), f1end = pKF1->mFeatVec.end();
+        typename std::remove_reference<decltype(pKF2->mFeatVec)>::type::const_iterator f2it = pKF2->mFeatVec.begin(), f2end = pKF2->mFeatVec.end();
+        while (f1it != f1end && f2it != f2end) {
+            if (f1it->first == f2it->first) {
+                for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+                    const size_t idx1 = f1it->second[i1];
+                    if (pKF1->GetMapPoint(idx1)) continue;
+                    const bool bStereo1 = pKF1->mvuRight[idx1] >= 0;
+                    if (bOnlyStereo && !bStereo1) continue;
+                    qIdx1.push_back((int)idx1);
+                    for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+                        const size_t idx2 = f2it->second[i2];
+                        if (pKF2->GetMapPoint(idx2)) continue;
+                        if (bOnlyStereo && !(pKF2->mvuRight[idx2] >= 0)) continue;
+                        cand.push_back((int)idx2);
+                    }
+                    offs.push_back((int)cand.size());
+                    const unsigned char *d = pKF1->mDescriptors.ptr((int)idx1);
+                    qDesc.insert(qDesc.end(), d, d + 32);
+                }
+                f1it++;
+                f2it++;
+            } else if (f1it->first < f2it->first) {
+                f1it = pKF1->mFeatVec.lower_bound(f2it->first);
+            } else {
+                f2it = pKF2->mFeatVec.lower_bound(f1it->first);
+            }
+        }
+        std::vector<uint16_t> dist;
+        if (!distances(qDesc, (int)qIdx1.size(), pKF2->mDescriptors, offs, cand, dist)) { vMatchedPairs.clear(); return 0; }
+        // epilogue (:762-835): note `dist > bestDist` -- a later candidate at an equal distance replaces an earlier one
+        for (size_t q = 0; q < qIdx1.size(); q++) {
+            const int idx1 = qIdx1[q];
+            const bool bStereo1 = pKF1->mvuRight[idx1] >= 0;
+            const cv::KeyPoint &kp1 = pKF1->mvKeysUn[idx1];
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const int idx2 = cand[c];
+                const int d = dist[c];
+                if (d > TH_LOW || d > bestDist) continue;
+                const cv::KeyPoint &kp2 = pKF2->mvKeysUn[idx2];
+                const bool bStereo2 = pKF2->mvuRight[idx2] >= 0;
+                if (!bStereo1 && !bStereo2) {
+                    const float distex = ex - kp2.pt.x;
+                    const float distey = ey - kp2.pt.y;
+                    if (distex * distex + distey * distey < 100 * pKF2->mvScaleFactors[kp2.octave]) continue;
+                }
+                if (CheckDistEpipolarLine(kp1, kp2, F12, pKF2)) { bestIdx2 = idx2; bestDist = d; }
+            }
+            if (bestIdx2 >= 0) {
+                const cv::KeyPoint &kp2 = pKF2->mvKeysUn[bestIdx2];
+                vMatches12[idx1] = bestIdx2;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = kp1.angle - kp2.angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(idx1);
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i == ind1 || i == ind2 || i == ind3) continue;
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    vMatches12[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve(nmatches);
+        for (size_t i = 0, iend = vMatches12.size(); i < iend; i++) {
+            if (vMatches12[i] < 0) continue;
+            vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
+        }
+        return nmatches;
+    }
+
     void SetDevice(int device) { device_ = device; } /* extension: GPU used by the searches (default: current) */
 
 public:
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;
+    static const int INT_MAX_ = 2147483647;
 
 protected:
     // one device call for all (query, candidate) pairs of a search

@@ -60,11 +60,18 @@ struct Frame {
 };
 
 struct KeyFrame {
+    int N = 0;
     std::vector<MapPoint *> mps;
     std::vector<cv::KeyPoint> mvKeysUn;
-    cv::Mat mDescriptors;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
+    cv::Mat mDescriptors, Rcw, tcw, Ow;
+    float fx = 718.856f, fy = 718.856f, cx = 320.f, cy = 240.f;
     std::map<unsigned int, std::vector<unsigned int>> mFeatVec;
     std::vector<MapPoint *> GetMapPointMatches() { return mps; }
+    MapPoint *GetMapPoint(const size_t &idx) { return mps[idx]; }
+    cv::Mat GetCameraCenter() { return Ow.clone(); }
+    cv::Mat GetRotation() { return Rcw.clone(); }
+    cv::Mat GetTranslation() { return tcw.clone(); }
 };
 
 static void fill_frame(Frame &F, int N)
@@ -278,7 +285,7 @@ int main()
         fill_frame(F, 1400);
         KeyFrame KF;
         const int NK = 1300;
-        KF.mvKeysUn.resize(NK); KF.mps.assign(NK, nullptr); KF.mDescriptors.create(NK, 32, CV_8U);
+        KF.N = NK; KF.mvKeysUn.resize(NK); KF.mps.assign(NK, nullptr); KF.mDescriptors.create(NK, 32, CV_8U);
         std::vector<MapPoint> store(NK);
         for (int i = 0; i < NK; i++) {
             const int src = rnd() % F.N;
@@ -339,6 +346,174 @@ int main()
         for (size_t i = 0; same && i < want.size(); i++) same = got[i] == want[i];
         printf("%s SearchByBoW(KeyFrame, Frame): %d matches (reference loop %d)\n", same && ng > 200 ? "ok" : "FAIL", ng, nr);
         fails += !(same && ng > 200);
+    }
+    // ---- M7: SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+    {
+        Frame F1, F2;
+        fill_frame(F1, 1600);
+        fill_frame(F2, 1600);
+        for (int i = 0; i < F1.N; i++) {
+            F1.mvKeys[i].octave = rnd() % 3 ? 0 : (int)(rnd() % 4);
+            const int j = (i * 7) % F2.N;
+            if (rnd() % 5) { // F2 holds a shifted, noisy copy of most F1 features; some targets are contested
+                F2.mvKeys[j].pt.x = F1.mvKeys[i].pt.x + (rndf() - 0.5f) * 60;
+                F2.mvKeys[j].pt.y = F1.mvKeys[i].pt.y + (rndf() - 0.5f) * 60;
+                F2.mvKeys[j].octave = rnd() % 6 ? 0 : 1;
+                F2.mvKeys[j].angle = std::fmod(F1.mvKeys[i].angle + (rnd() % 8 ? 3.f : 200.f * rndf()), 360.f);
+                noisy_copy(F1.mDescriptors.ptr(i), F2.mDescriptors.ptr(j), rnd() % 50);
+            }
+        }
+        for (int i = 0; i + 3 < F1.N; i += 11) { memcpy(F1.mDescriptors.ptr(i + 3), F1.mDescriptors.ptr(i), 32); F1.mvKeys[i + 3].pt = F1.mvKeys[i].pt; F1.mvKeys[i + 3].octave = F1.mvKeys[i].octave; }
+        F1.mvKeysUn = F1.mvKeys; F2.mvKeysUn = F2.mvKeys;
+        std::vector<cv::Point2f> prevG(F1.N), prevR(F1.N);
+        for (int i = 0; i < F1.N; i++) prevG[i] = prevR[i] = F1.mvKeysUn[i].pt;
+        std::vector<int> gotM, wantM(F1.N, -1);
+        ORB_SLAM2::ORBmatcher matcher(0.9f, true);
+        const int ng = matcher.SearchForInitialization(F1, F2, prevG, gotM, 100);
+        int nr = 0;
+        {
+            std::vector<int> rotHist[30], vMatchedDistance(F2.N, 2147483647), vnMatches21(F2.N, -1);
+            for (int i1 = 0; i1 < F1.N; i1++) {
+                if (F1.mvKeysUn[i1].octave > 0) continue;
+                std::vector<size_t> vi = F2.GetFeaturesInArea(prevR[i1].x, prevR[i1].y, 100, 0, 0);
+                if (vi.empty()) continue;
+                int bestDist = 2147483647, bestDist2 = 2147483647, bestIdx2 = -1;
+                for (size_t i2 : vi) {
+                    const int d = ref_descriptor_distance(F1.mDescriptors.ptr(i1), F2.mDescriptors.ptr((int)i2));
+                    if (vMatchedDistance[i2] <= d) continue;
+                    if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = (int)i2; } else if (d < bestDist2) bestDist2 = d;
+                }
+                if (bestDist <= 50 && bestDist < (float)bestDist2 * 0.9f) {
+                    if (vnMatches21[bestIdx2] >= 0) { wantM[vnMatches21[bestIdx2]] = -1; nr--; }
+                    wantM[i1] = bestIdx2; vnMatches21[bestIdx2] = i1; vMatchedDistance[bestIdx2] = bestDist; nr++;
+                    float rot = F1.mvKeysUn[i1].angle - F2.mvKeysUn[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * (1.0f / 30));
+                    if (bin == 30) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+            int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                const int sz = (int)rotHist[i].size();
+                if (sz > m1) { m3 = m2; m2 = m1; m1 = sz; i3 = i2; i2 = i1; i1 = i; }
+                else if (sz > m2) { m3 = m2; m2 = sz; i3 = i2; i2 = i; }
+                else if (sz > m3) { m3 = sz; i3 = i; }
+            }
+            if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; } else if (m3 < 0.1f * (float)m1) i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                if (i == i1 || i == i2 || i == i3) continue;
+                for (int idx1 : rotHist[i]) if (wantM[idx1] >= 0) { wantM[idx1] = -1; nr--; }
+            }
+            for (int i = 0; i < F1.N; i++) if (wantM[i] >= 0) prevR[i] = F2.mvKeysUn[wantM[i]].pt;
+        }
+        bool same = ng == nr && gotM == wantM;
+        for (int i = 0; same && i < F1.N; i++) same = prevG[i].x == prevR[i].x && prevG[i].y == prevR[i].y;
+        printf("%s SearchForInitialization: %d matches (reference loop %d)\n", same && ng > 150 ? "ok" : "FAIL", ng, nr);
+        fails += !(same && ng > 150);
+    }
+    // ---- M8: SearchForTriangulation(KF1, KF2, F12, pairs, bOnlyStereo)
+    for (int onlyStereo = 0; onlyStereo < 2; onlyStereo++) {
+        KeyFrame K1, K2;
+        Frame tmp;
+        fill_frame(tmp, 1400);
+        std::vector<MapPoint> store(8);
+        for (KeyFrame *K : {&K1, &K2}) {
+            K->N = tmp.N; K->mps.assign(K->N, nullptr); K->mvuRight.assign(K->N, -1.f);
+            K->mvScaleFactors = tmp.mvScaleFactors;
+            for (float f : K->mvScaleFactors) K->mvLevelSigma2.push_back(f * f);
+            K->mDescriptors.create(K->N, 32, CV_8U);
+            K->Rcw.create(3, 3, CV_32F); K->tcw.create(3, 1, CV_32F); K->Ow.create(3, 1, CV_32F);
+            for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) K->Rcw.at<float>(r, c) = r == c; K->tcw.at<float>(r, 0) = 0; K->Ow.at<float>(r, 0) = 0; }
+        }
+        K2.tcw.at<float>(0, 0) = -0.5f; K2.tcw.at<float>(2, 0) = 0.3f; K2.Ow.at<float>(0, 0) = 0.5f; K2.Ow.at<float>(2, 0) = -0.3f;
+        K1.mvKeysUn = tmp.mvKeys; K2.mvKeysUn.resize(tmp.N);
+        for (int i = 0; i < tmp.N; i++) {
+            memcpy(K1.mDescriptors.ptr(i), tmp.mDescriptors.ptr(i), 32);
+            K2.mvKeysUn[i] = tmp.mvKeys[i];
+            K2.mvKeysUn[i].pt.x += (rndf() - 0.5f) * 80;
+            K2.mvKeysUn[i].pt.y += rnd() % 4 ? (rndf() - 0.5f) * 2.f : (rndf() - 0.5f) * 30.f; // epipolar lines are image rows
+            K2.mvKeysUn[i].angle = std::fmod(tmp.mvKeys[i].angle + (rnd() % 8 ? 4.f : 150.f * rndf()), 360.f);
+            noisy_copy(tmp.mDescriptors.ptr(i), K2.mDescriptors.ptr(i), rnd() % 70);
+            if (rnd() % 3 == 0) K1.mvuRight[i] = 10.f;
+            if (rnd() % 3 == 0) K2.mvuRight[i] = 10.f;
+            if (rnd() % 10 == 0) K1.mps[i] = &store[i % 8];
+            if (rnd() % 10 == 0) K2.mps[i] = &store[i % 8];
+            const unsigned node = (unsigned)(i % 53) * 2;
+            K1.mFeatVec[node].push_back(i);
+            K2.mFeatVec[rnd() % 12 ? node : node + 2].push_back(i);
+        }
+        for (int i = 0; i + 53 < tmp.N; i += 9) memcpy(K2.mDescriptors.ptr(i + 53), K2.mDescriptors.ptr(i), 32), K2.mvKeysUn[i + 53].pt.y = K2.mvKeysUn[i].pt.y; // equal distances in one node
+        cv::Mat F12(3, 3, CV_32F);
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) F12.at<float>(r, c) = 0;
+        F12.at<float>(1, 2) = -1.f; F12.at<float>(2, 1) = 1.f;
+        std::vector<std::pair<size_t, size_t>> got, want;
+        ORB_SLAM2::ORBmatcher matcher(0.6f, false), matcherOri(0.6f, true);
+        ORB_SLAM2::ORBmatcher &mm = onlyStereo ? matcherOri : matcher;
+        const int ng = mm.SearchForTriangulation(&K1, &K2, F12, got, onlyStereo != 0);
+        int nr = 0;
+        {
+            const float C2[3] = {K2.tcw.at<float>(0, 0), K2.tcw.at<float>(1, 0), K2.tcw.at<float>(2, 0)}; // R2w = I, Cw = 0
+            const float invz = 1.0f / C2[2], ex = K2.fx * C2[0] * invz + K2.cx, ey = K2.fy * C2[1] * invz + K2.cy;
+            std::vector<int> vM(K1.N, -1), rotHist[30];
+            auto f1 = K1.mFeatVec.begin(); auto f2 = K2.mFeatVec.begin();
+            while (f1 != K1.mFeatVec.end() && f2 != K2.mFeatVec.end()) {
+                if (f1->first == f2->first) {
+                    for (unsigned idx1 : f1->second) {
+                        if (K1.mps[idx1]) continue;
+                        const bool s1 = K1.mvuRight[idx1] >= 0;
+                        if (onlyStereo && !s1) continue;
+                        const cv::KeyPoint &kp1 = K1.mvKeysUn[idx1];
+                        int bestDist = 50, bestIdx2 = -1;
+                        for (unsigned idx2 : f2->second) {
+                            if (K2.mps[idx2]) continue;
+                            const bool s2 = K2.mvuRight[idx2] >= 0;
+                            if (onlyStereo && !s2) continue;
+                            const int d = ref_descriptor_distance(K1.mDescriptors.ptr((int)idx1), K2.mDescriptors.ptr((int)idx2));
+                            if (d > 50 || d > bestDist) continue;
+                            const cv::KeyPoint &kp2 = K2.mvKeysUn[idx2];
+                            if (!s1 && !s2) {
+                                const float dx = ex - kp2.pt.x, dy = ey - kp2.pt.y;
+                                if (dx * dx + dy * dy < 100 * K2.mvScaleFactors[kp2.octave]) continue;
+                            }
+                            const float a = kp1.pt.x * 0 + kp1.pt.y * 0 + 0, b = kp1.pt.x * 0 + kp1.pt.y * 0 + 1.f, c = kp1.pt.x * 0 + kp1.pt.y * -1.f + 0;
+                            const float num = a * kp2.pt.x + b * kp2.pt.y + c, den = a * a + b * b;
+                            if (den == 0) continue;
+                            if (num * num / den < 3.84 * K2.mvLevelSigma2[kp2.octave]) { bestIdx2 = (int)idx2; bestDist = d; }
+                        }
+                        if (bestIdx2 >= 0) {
+                            vM[idx1] = bestIdx2; nr++;
+                            float rot = kp1.angle - K2.mvKeysUn[bestIdx2].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * (1.0f / 30));
+                            if (bin == 30) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                        }
+                    }
+                    f1++; f2++;
+                } else if (f1->first < f2->first) f1 = K1.mFeatVec.lower_bound(f2->first);
+                else f2 = K2.mFeatVec.lower_bound(f1->first);
+            }
+            if (onlyStereo) { // this run checks orientation
+                int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;
+                for (int i = 0; i < 30; i++) {
+                    const int sz = (int)rotHist[i].size();
+                    if (sz > m1) { m3 = m2; m2 = m1; m1 = sz; i3 = i2; i2 = i1; i1 = i; }
+                    else if (sz > m2) { m3 = m2; m2 = sz; i3 = i2; i2 = i; }
+                    else if (sz > m3) { m3 = sz; i3 = i; }
+                }
+                if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; } else if (m3 < 0.1f * (float)m1) i3 = -1;
+                for (int i = 0; i < 30; i++) {
+                    if (i == i1 || i == i2 || i == i3) continue;
+                    for (int j : rotHist[i]) { vM[j] = -1; nr--; }
+                }
+            }
+            for (int i = 0; i < K1.N; i++) if (vM[i] >= 0) want.push_back(std::make_pair((size_t)i, (size_t)vM[i]));
+        }
+        const bool same = ng == nr && got == want;
+        const int need = onlyStereo ? 20 : 150;
+        printf("%s SearchForTriangulation(bOnlyStereo=%d): %d pairs (reference loop %d)\n", same && ng > need ? "ok" : "FAIL", onlyStereo, ng, nr);
+        fails += !(same && ng > need);
     }
     // ---- M1: static DescriptorDistance
     {
