@@ -466,6 +466,185 @@ public:
         return nmatches;
     }
 
+    // Fuse map points into a keyframe (src/ORBmatcher.cc:873-1038; callers src/LocalMapping.cc:553, 579).
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT *pKF, const std::vector<MapPointT *> &vpMapPoints, const float th = 3.0)
+    {
+        const cv::Mat Rm = pKF->GetRotation(), tm = pKF->GetTranslation(), Om = pKF->GetCameraCenter();
+        float Rcw[9], tcw[3], Ow[3];
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) Rcw[3 * r + c] = Rm.template at<float>(r, c);
+            tcw[r] = tm.template at<float>(r, 0);
+            Ow[r] = Om.template at<float>(r, 0);
+        }
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy, bf = pKF->mbf;
+        // prologue (:892-943): projection, distance / viewing-angle gates, predicted level -> one window per map point
+        std::vector<int> qI, qLevel;
+        std::vector<float> qU, qV, qUr, windows;
+        std::vector<unsigned char> qDesc;
+        const int nMPs = (int)vpMapPoints.size();
+        for (int i = 0; i < nMPs; i++) {
+            MapPointT *pMP = vpMapPoints[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            const cv::Mat p3Dw = pMP->GetWorldPos();
+            const float pw[3] = {p3Dw.template at<float>(0, 0), p3Dw.template at<float>(1, 0), p3Dw.template at<float>(2, 0)};
+            float p3Dc[3];
+            mat_Rx_t(Rcw, pw, tcw, p3Dc);
+            if (p3Dc[2] < 0.0f) continue;
+            const float invz = 1 / p3Dc[2];
+            const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            const float ur = u - bf * invz;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            const float PO[3] = {pw[0] - Ow[0], pw[1] - Ow[1], pw[2] - Ow[2]};
+            const float dist3D = (float)std::sqrt((double)PO[0] * PO[0] + (double)PO[1] * PO[1] + (double)PO[2] * PO[2]); // cv::norm
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            const cv::Mat Pn = pMP->GetNormal();
+            const double dot = (double)PO[0] * Pn.template at<float>(0, 0) + (double)PO[1] * Pn.template at<float>(1, 0) +
+                               (double)PO[2] * Pn.template at<float>(2, 0); // cv::Mat::dot
+            if (dot < 0.5 * dist3D) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+            const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+            qI.push_back(i); qLevel.push_back(nPredictedLevel); qU.push_back(u); qV.push_back(v); qUr.push_back(ur);
+            const float wq[5] = {u, v, radius, -1.f, -1.f}; // KeyFrame::GetFeaturesInArea has no level filter (KeyFrame.cc:607)
+            windows.insert(windows.end(), wq, wq + 5);
+            const cv::Mat d = pMP->GetDescriptor();
+            qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search(pKF->mvKeysUn, pKF->mDescriptors, pKF->mnMinX, pKF->mnMinY, pKF->mfGridElementWidthInv,
+                           pKF->mfGridElementHeightInv, pKF->mnGridCols, pKF->mnGridRows, windows, qDesc, offs, cand, dist))
+            return 0;
+        // epilogue (:945-1034), in map-point order; the graph mutations of earlier iterations are re-checked
+        int nFused = 0;
+        for (size_t q = 0; q < qI.size(); q++) {
+            MapPointT *pMP = vpMapPoints[qI[q]];
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            const int nPredictedLevel = qLevel[q];
+            const float u = qU[q], v = qV[q], ur = qUr[q];
+            int bestDist = 256, bestIdx = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t idx = (size_t)cand[c];
+                const cv::KeyPoint &kp = pKF->mvKeysUn[idx];
+                const int kpLevel = kp.octave;
+                if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+                if (pKF->mvuRight[idx] >= 0) {
+                    const float ex = u - kp.pt.x, ey = v - kp.pt.y, er = ur - pKF->mvuRight[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * pKF->mvInvLevelSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float ex = u - kp.pt.x, ey = v - kp.pt.y;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * pKF->mvInvLevelSigma2[kpLevel] > 5.99) continue;
+                }
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+            }
+            if (bestDist <= TH_LOW) {
+                MapPointT *pMPinKF = pKF->GetMapPoint(bestIdx);
+                if (pMPinKF) {
+                    if (!pMPinKF->isBad()) {
+                        if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                        else pMPinKF->Replace(pMP);
+                    }
+                } else {
+                    pMP->AddObservation(pKF, bestIdx);
+                    pKF->AddMapPoint(pMP, bestIdx);
+                }
+                nFused++;
+            }
+        }
+        return nFused;
+    }
+
+    // Loop-closure matching between two keyframes (src/ORBmatcher.cc:568-702; caller src/LoopClosing.cc:323).
+    template <class KeyFrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT *pKF1, KeyFrameT *pKF2, std::vector<MapPointT *> &vpMatches12)
+    {
+        const std::vector<cv::KeyPoint> &vKeysUn1 = pKF1->mvKeysUn, &vKeysUn2 = pKF2->mvKeysUn;
+        const std::vector<MapPointT *> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        vpMatches12 = std::vector<MapPointT *>(vpMapPoints1.size(), static_cast<MapPointT *>(NULL));
+        std::vector<bool> vbMatched2(vpMapPoints2.size(), false);
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        int nmatches = 0;
+        // prologue: merge walk (:590-679); candidates = features of the same node holding a good map point
+        std::vector<int> qIdx1, offs(1, 0), cand;
+        std::vector<unsigned char> qDesc;
+        typename std::remove_reference<decltype(pKF1->mFeatVec)>::type::const_iterator f1it = pKF1->mFeatVec.begin(), f1end = pKF1->mFeatVec.end();
+        typename std::remove_reference<decltype(pKF2->mFeatVec)>::type::const_iterator f2it = pKF2->mFeatVec.begin(), f2end = pKF2->mFeatVec.end();
+        while (f1it != f1end && f2it != f2end) {
+            if (f1it->first == f2it->first) {
+                for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+                    const size_t idx1 = f1it->second[i1];
+                    MapPointT *pMP1 = vpMapPoints1[idx1];
+                    if (!pMP1) continue;
+                    if (pMP1->isBad()) continue;
+                    qIdx1.push_back((int)idx1);
+                    for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+                        const size_t idx2 = f2it->second[i2];
+                        MapPointT *pMP2 = vpMapPoints2[idx2];
+                        if (!pMP2) continue;
+                        if (pMP2->isBad()) continue;
+                        cand.push_back((int)idx2);
+                    }
+                    offs.push_back((int)cand.size());
+                    const unsigned char *d = pKF1->mDescriptors.ptr((int)idx1);
+                    qDesc.insert(qDesc.end(), d, d + 32);
+                }
+                f1it++;
+                f2it++;
+            } else if (f1it->first < f2it->first) {
+                f1it = pKF1->mFeatVec.lower_bound(f2it->first);
+            } else {
+                f2it = pKF2->mFeatVec.lower_bound(f1it->first);
+            }
+        }
+        std::vector<uint16_t> dist;
+        if (!distances(qDesc, (int)qIdx1.size(), pKF2->mDescriptors, offs, cand, dist)) return 0;
+        // epilogue (:606-668): strict `<` on TH_LOW here, unlike the Frame overload
+        for (size_t q = 0; q < qIdx1.size(); q++) {
+            const int idx1 = qIdx1[q];
+            int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const int idx2 = cand[c];
+                if (vbMatched2[idx2]) continue;
+                const int d = dist[c];
+                if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdx2 = idx2; }
+                else if (d < bestDist2) bestDist2 = d;
+            }
+            if (bestDist1 < TH_LOW) {
+                if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                    vpMatches12[idx1] = vpMapPoints2[bestIdx2];
+                    vbMatched2[bestIdx2] = true;
+                    if (mbCheckOrientation) {
+                        float rot = vKeysUn1[idx1].angle - vKeysUn2[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back(idx1);
+                    }
+                    nmatches++;
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i == ind1 || i == ind2 || i == ind3) continue;
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    vpMatches12[rotHist[i][j]] = static_cast<MapPointT *>(NULL);
+                    nmatches--;
+                }
+            }
+        }
+        return nmatches;
+    }
+
     void SetDevice(int device) { device_ = device; } /* extension: GPU used by the searches (default: current) */
 
 public:

@@ -21,7 +21,25 @@ static unsigned long long g_s = 88172645463325252ull;
 static unsigned rnd() { g_s ^= g_s << 13; g_s ^= g_s >> 7; g_s ^= g_s << 17; return (unsigned)(g_s >> 11); }
 static float rndf() { return (rnd() & 0xFFFFFF) / (float)0x1000000; }
 
+struct KeyFrame;
 struct MapPoint {
+    // Fuse-related state (src/MapPoint.cc): observations, replacement, distance invariance, normal, scale prediction
+    float maxDist = 1e9f, minDist = 0.f;
+    cv::Mat normal;
+    MapPoint *replacedBy = nullptr;
+    std::vector<std::pair<KeyFrame *, size_t>> observations;
+    bool IsInKeyFrame(KeyFrame *kf) { for (auto &o : observations) if (o.first == kf) return true; return false; }
+    float GetMaxDistanceInvariance() { return 1.2f * maxDist; }
+    float GetMinDistanceInvariance() { return 0.8f * minDist; }
+    cv::Mat GetNormal() { return normal.clone(); }
+    int PredictScale(const float &currentDist, KeyFrame *) {
+        const float ratio = maxDist / currentDist;
+        int nScale = (int)std::ceil(std::log(ratio) / std::log(1.2f));
+        if (nScale < 0) nScale = 0; else if (nScale >= 8) nScale = 7;
+        return nScale;
+    }
+    void Replace(MapPoint *other) { bad = true; replacedBy = other; }
+    void AddObservation(KeyFrame *kf, size_t idx) { observations.push_back(std::make_pair(kf, idx)); obs++; }
     bool mbTrackInView = true, bad = false;
     int mnTrackScaleLevel = 0, obs = 1;
     float mTrackViewCos = 1.f, mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0;
@@ -65,8 +83,27 @@ struct KeyFrame {
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
     cv::Mat mDescriptors, Rcw, tcw, Ow;
-    float fx = 718.856f, fy = 718.856f, cx = 320.f, cy = 240.f;
+    float fx = 718.856f, fy = 718.856f, cx = 320.f, cy = 240.f, mbf = 386.1448f;
+    float mnMinX = 0, mnMinY = 0, mnMaxX = 640, mnMaxY = 480, mfGridElementWidthInv = 64.f / 640.f, mfGridElementHeightInv = 48.f / 480.f;
+    int mnGridCols = 64, mnGridRows = 48;
+    std::vector<float> mvInvLevelSigma2;
     std::map<unsigned int, std::vector<unsigned int>> mFeatVec;
+    bool IsInImage(const float &x, const float &y) const { return (x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY); }
+    void AddMapPoint(MapPoint *pMP, const size_t &idx) { mps[idx] = pMP; }
+    // KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:607-647) through the CPU oracle: same grid walk, no level filter
+    mutable std::vector<int> cellStart, cellItems;
+    std::vector<size_t> GetFeaturesInArea(const float &x, const float &y, const float &r) const
+    {
+        if (cellStart.empty()) {
+            cellStart.assign(64 * 48 + 1, 0);
+            cellItems.assign(N > 0 ? N : 1, 0);
+            ref_assign_grid(mvKeysUn.data(), N, mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv, 64, 48, cellStart.data(), cellItems.data());
+        }
+        std::vector<int> out(N > 0 ? N : 1);
+        const int n = ref_features_in_area(mvKeysUn.data(), cellStart.data(), cellItems.data(), mnMinX, mnMinY, mfGridElementWidthInv,
+                                           mfGridElementHeightInv, 64, 48, x, y, r, -1, -1, out.data(), (int)out.size());
+        return std::vector<size_t>(out.begin(), out.begin() + n);
+    }
     std::vector<MapPoint *> GetMapPointMatches() { return mps; }
     MapPoint *GetMapPoint(const size_t &idx) { return mps[idx]; }
     cv::Mat GetCameraCenter() { return Ow.clone(); }
@@ -514,6 +551,171 @@ int main()
         const int need = onlyStereo ? 20 : 150;
         printf("%s SearchForTriangulation(bOnlyStereo=%d): %d pairs (reference loop %d)\n", same && ng > need ? "ok" : "FAIL", onlyStereo, ng, nr);
         fails += !(same && ng > need);
+    }
+    // ---- M9: Fuse(KeyFrame, MapPoints, th)
+    {
+        Frame tmp;
+        fill_frame(tmp, 1500);
+        const int NP = 1300;
+        KeyFrame KA, KB;
+        std::vector<MapPoint> storeA(NP + tmp.N), storeB;
+        for (KeyFrame *K : {&KA, &KB}) {
+            K->N = tmp.N; K->mps.assign(K->N, nullptr); K->mvuRight = tmp.mvuRight; K->mvKeysUn = tmp.mvKeys;
+            K->mvScaleFactors = tmp.mvScaleFactors;
+            for (float f : K->mvScaleFactors) { K->mvLevelSigma2.push_back(f * f); K->mvInvLevelSigma2.push_back(1.0f / (f * f)); }
+            K->mDescriptors = tmp.mDescriptors.clone();
+            K->Rcw.create(3, 3, CV_32F); K->tcw.create(3, 1, CV_32F); K->Ow.create(3, 1, CV_32F);
+            for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) K->Rcw.at<float>(r, c) = r == c; K->tcw.at<float>(r, 0) = 0; K->Ow.at<float>(r, 0) = 0; }
+        }
+        for (int i = 0; i < NP; i++) { // candidates to fuse: 3-D points projecting near keyframe features
+            MapPoint &m = storeA[i];
+            const int src = rnd() % tmp.N;
+            const float z = 3.f + 20.f * rndf();
+            const float u = tmp.mvKeys[src].pt.x + (rndf() - 0.5f) * 3, v = tmp.mvKeys[src].pt.y + (rndf() - 0.5f) * 3;
+            m.pos.create(3, 1, CV_32F);
+            m.pos.at<float>(0, 0) = (u - KA.cx) * z / KA.fx; m.pos.at<float>(1, 0) = (v - KA.cy) * z / KA.fy; m.pos.at<float>(2, 0) = rnd() % 40 ? z : -z;
+            m.normal.create(3, 1, CV_32F);
+            const float nn = std::sqrt(m.pos.at<float>(0, 0) * m.pos.at<float>(0, 0) + m.pos.at<float>(1, 0) * m.pos.at<float>(1, 0) + z * z);
+            for (int r = 0; r < 3; r++) m.normal.at<float>(r, 0) = (rnd() % 15 ? 1.f : -1.f) * m.pos.at<float>(r, 0) / nn;
+            m.maxDist = nn * std::pow(1.2f, (float)tmp.mvKeys[src].octave) * (0.9f + 0.2f * rndf());
+            m.minDist = m.maxDist / std::pow(1.2f, 7.f);
+            m.desc.create(1, 32, CV_8U);
+            noisy_copy(tmp.mDescriptors.ptr(src), m.desc.ptr(), rnd() % 70);
+            m.obs = 1 + rnd() % 5;
+            m.bad = rnd() % 30 == 0;
+        }
+        for (int j = 0; j < tmp.N; j++) { // some keyframe features already hold a map point (-> Replace either way)
+            MapPoint &m = storeA[NP + j];
+            m.obs = 1 + rnd() % 5; m.bad = rnd() % 20 == 0;
+        }
+        storeB = storeA;
+        for (size_t i = 0; i < storeB.size(); i++) { storeB[i].desc = storeA[i].desc.clone(); }
+        std::vector<MapPoint *> vpA, vpB;
+        for (int i = 0; i < NP; i++) { vpA.push_back(rnd() % 50 ? &storeA[i] : nullptr); vpB.push_back(vpA.back() ? &storeB[i] : nullptr); }
+        for (int i = 5; i < NP; i += 40) { vpA[i] = vpA[i - 3]; vpB[i] = vpB[i - 3]; } // duplicates: IsInKeyFrame after the first fuse
+        for (int j = 0; j < tmp.N; j++) if (rnd() % 3 == 0) { KA.mps[j] = &storeA[NP + j]; KB.mps[j] = &storeB[NP + j]; storeA[NP + j].observations.push_back({&KA, (size_t)j}); storeB[NP + j].observations.push_back({&KB, (size_t)j}); }
+        for (int j = 0; j < tmp.N; j += 17) if (KA.mps[j]) { vpA.push_back(KA.mps[j]); vpB.push_back(KB.mps[j]); } // points that get replaced appear later in the list
+        ORB_SLAM2::ORBmatcher matcher;
+        const int ng = matcher.Fuse(&KA, vpA, 3.0f);
+        int nr = 0;
+        { // reference loop (src/ORBmatcher.cc:873-1038) on copy B with the oracle's distance and grid
+            KeyFrame *pKF = &KB;
+            for (size_t i = 0; i < vpB.size(); i++) {
+                MapPoint *pMP = vpB[i];
+                if (!pMP) continue;
+                if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+                const float X = pMP->pos.at<float>(0, 0), Y = pMP->pos.at<float>(1, 0), Z = pMP->pos.at<float>(2, 0);
+                if (Z < 0.0f) continue; // Rcw = I, tcw = 0
+                const float invz = 1 / Z, x = X * invz, y = Y * invz, u = pKF->fx * x + pKF->cx, v = pKF->fy * y + pKF->cy;
+                if (!pKF->IsInImage(u, v)) continue;
+                const float ur = u - pKF->mbf * invz;
+                const float dist3D = (float)std::sqrt((double)X * X + (double)Y * Y + (double)Z * Z);
+                if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+                const double dot = (double)X * pMP->normal.at<float>(0, 0) + (double)Y * pMP->normal.at<float>(1, 0) + (double)Z * pMP->normal.at<float>(2, 0);
+                if (dot < 0.5 * dist3D) continue;
+                const int lvl = pMP->PredictScale(dist3D, pKF);
+                const float radius = 3.0f * pKF->mvScaleFactors[lvl];
+                const std::vector<size_t> vi = pKF->GetFeaturesInArea(u, v, radius);
+                if (vi.empty()) continue;
+                int bestDist = 256, bestIdx = -1;
+                for (size_t idx : vi) {
+                    const cv::KeyPoint &kp = pKF->mvKeysUn[idx];
+                    if (kp.octave < lvl - 1 || kp.octave > lvl) continue;
+                    if (pKF->mvuRight[idx] >= 0) {
+                        const float ex = u - kp.pt.x, ey = v - kp.pt.y, er = ur - pKF->mvuRight[idx];
+                        if ((ex * ex + ey * ey + er * er) * pKF->mvInvLevelSigma2[kp.octave] > 7.8) continue;
+                    } else {
+                        const float ex = u - kp.pt.x, ey = v - kp.pt.y;
+                        if ((ex * ex + ey * ey) * pKF->mvInvLevelSigma2[kp.octave] > 5.99) continue;
+                    }
+                    const int d = ref_descriptor_distance(pMP->desc.ptr(), pKF->mDescriptors.ptr((int)idx));
+                    if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+                }
+                if (bestDist <= 50) {
+                    MapPoint *in = pKF->GetMapPoint(bestIdx);
+                    if (in) { if (!in->isBad()) { if (in->Observations() > pMP->Observations()) pMP->Replace(in); else in->Replace(pMP); } }
+                    else { pMP->AddObservation(pKF, bestIdx); pKF->AddMapPoint(pMP, bestIdx); }
+                    nr++;
+                }
+            }
+        }
+        bool same = ng == nr;
+        for (int j = 0; same && j < tmp.N; j++) same = (KA.mps[j] ? KA.mps[j] - storeA.data() : -1) == (KB.mps[j] ? KB.mps[j] - storeB.data() : -1);
+        for (size_t i = 0; same && i < storeA.size(); i++)
+            same = storeA[i].bad == storeB[i].bad && storeA[i].obs == storeB[i].obs &&
+                   (storeA[i].replacedBy ? storeA[i].replacedBy - storeA.data() : -1) == (storeB[i].replacedBy ? storeB[i].replacedBy - storeB.data() : -1);
+        printf("%s Fuse(KeyFrame, MapPoints): %d fused (reference loop %d)\n", same && ng > 300 ? "ok" : "FAIL", ng, nr);
+        fails += !(same && ng > 300);
+    }
+    // ---- M6b: SearchByBoW(KeyFrame, KeyFrame)
+    {
+        Frame tmp;
+        fill_frame(tmp, 1300);
+        KeyFrame K1, K2;
+        std::vector<MapPoint> s1(tmp.N), s2(tmp.N);
+        for (KeyFrame *K : {&K1, &K2}) { K->N = tmp.N; K->mps.assign(K->N, nullptr); K->mvKeysUn = tmp.mvKeys; K->mDescriptors.create(K->N, 32, CV_8U); }
+        for (int i = 0; i < tmp.N; i++) {
+            memcpy(K1.mDescriptors.ptr(i), tmp.mDescriptors.ptr(i), 32);
+            noisy_copy(tmp.mDescriptors.ptr(i), K2.mDescriptors.ptr(i), rnd() % 64);
+            K2.mvKeysUn[i].angle = std::fmod(tmp.mvKeys[i].angle + (rnd() % 8 ? 6.f : 180.f * rndf()), 360.f);
+            if (rnd() % 5) { K1.mps[i] = &s1[i]; s1[i].bad = rnd() % 25 == 0; }
+            if (rnd() % 5) { K2.mps[i] = &s2[i]; s2[i].bad = rnd() % 25 == 0; }
+            const unsigned node = (unsigned)(i % 61) * 2;
+            K1.mFeatVec[node].push_back(i);
+            K2.mFeatVec[rnd() % 10 ? node : node + 2].push_back(i);
+        }
+        for (int i = 0; i + 61 < tmp.N; i += 7) memcpy(K2.mDescriptors.ptr(i + 61), K2.mDescriptors.ptr(i), 32);
+        std::vector<MapPoint *> got, want(tmp.N, nullptr);
+        ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+        const int ng = matcher.SearchByBoW(&K1, &K2, got);
+        int nr = 0;
+        {
+            std::vector<bool> vbMatched2(tmp.N, false);
+            std::vector<int> rotHist[30];
+            auto f1 = K1.mFeatVec.begin(); auto f2 = K2.mFeatVec.begin();
+            while (f1 != K1.mFeatVec.end() && f2 != K2.mFeatVec.end()) {
+                if (f1->first == f2->first) {
+                    for (unsigned idx1 : f1->second) {
+                        MapPoint *p1 = K1.mps[idx1];
+                        if (!p1 || p1->isBad()) continue;
+                        int b1 = 256, bi = -1, b2 = 256;
+                        for (unsigned idx2 : f2->second) {
+                            MapPoint *p2 = K2.mps[idx2];
+                            if (vbMatched2[idx2] || !p2) continue;
+                            if (p2->isBad()) continue;
+                            const int d = ref_descriptor_distance(K1.mDescriptors.ptr((int)idx1), K2.mDescriptors.ptr((int)idx2));
+                            if (d < b1) { b2 = b1; b1 = d; bi = (int)idx2; } else if (d < b2) b2 = d;
+                        }
+                        if (b1 < 50 && (float)b1 < 0.75f * (float)b2) {
+                            want[idx1] = K2.mps[bi]; vbMatched2[bi] = true;
+                            float rot = K1.mvKeysUn[idx1].angle - K2.mvKeysUn[bi].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * (1.0f / 30));
+                            if (bin == 30) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                            nr++;
+                        }
+                    }
+                    f1++; f2++;
+                } else if (f1->first < f2->first) f1 = K1.mFeatVec.lower_bound(f2->first);
+                else f2 = K2.mFeatVec.lower_bound(f1->first);
+            }
+            int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                const int sz = (int)rotHist[i].size();
+                if (sz > m1) { m3 = m2; m2 = m1; m1 = sz; i3 = i2; i2 = i1; i1 = i; }
+                else if (sz > m2) { m3 = m2; m2 = sz; i3 = i2; i2 = i; }
+                else if (sz > m3) { m3 = sz; i3 = i; }
+            }
+            if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; } else if (m3 < 0.1f * (float)m1) i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                if (i == i1 || i == i2 || i == i3) continue;
+                for (int j : rotHist[i]) { want[j] = nullptr; nr--; }
+            }
+        }
+        const bool same = ng == nr && got == want;
+        printf("%s SearchByBoW(KeyFrame, KeyFrame): %d matches (reference loop %d)\n", same && ng > 200 ? "ok" : "FAIL", ng, nr);
+        fails += !(same && ng > 200);
     }
     // ---- M1: static DescriptorDistance
     {
