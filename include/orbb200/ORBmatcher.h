@@ -14,9 +14,9 @@
  * tree they bind to ORB_SLAM2::Frame etc. (same member names: mvKeysUn, mDescriptors, mvpMapPoints, mFeatVec, ...),
  * and this repo's tests bind them to small stand-ins (tests/cpp/facade_match.cpp).  The windowed searches send
  * their windows to orbb200_window_search (grid build + GetFeaturesInArea + distances on the device); the BoW-node
- * searches send CSR lists to orbb200_candidate_distances.  Not yet in this header: the Sim3 / relocalisation
- * overloads (SearchByProjection(KF, Scw, ...), SearchByProjection(F, KF, sFound, ...), SearchBySim3, Fuse): they are
- * the same prologue / device call / epilogue over a KeyFrame grid; see INTEGRATION.md 4.
+ * searches send CSR lists to orbb200_candidate_distances.  All twelve public searches of the reference class are here
+ * (M1-M9 of SURVEY.md 8a plus the Sim3 overloads of loop closing); pose arithmetic on the host follows cv::gemm /
+ * cv::norm / Mat::dot for CV_32F (double accumulation, one narrowing) so projections agree to the bit.
  */
 #ifndef ORBB200_ORBMATCHER_H
 #define ORBB200_ORBMATCHER_H
@@ -25,6 +25,7 @@
 #include <cstdint>
 #include <cstring>
 #include <iostream>
+#include <set>
 #include <type_traits>
 #include <utility>
 #include <vector>
@@ -560,6 +561,235 @@ public:
         return nFused;
     }
 
+    // Relocalisation: project the map points of a candidate keyframe into the current frame
+    // (src/ORBmatcher.cc:1555-1685; caller src/Tracking.cc:1504, 1518).
+    template <class FrameT, class KeyFrameT, class SetT>
+    int SearchByProjection(FrameT &CurrentFrame, KeyFrameT *pKF, const SetT &sAlreadyFound, const float th, const int ORBdist)
+    {
+        typedef typename std::remove_pointer<typename std::remove_reference<decltype(CurrentFrame.mvpMapPoints[0])>::type>::type MapPointT;
+        int nmatches = 0;
+        float Rcw[9], tcw[3], Ow[3];
+        pose_Rt(CurrentFrame.mTcw, Rcw, tcw);
+        camera_centre(Rcw, tcw, Ow);
+        std::vector<int> rotHist[HISTO_LENGTH];
+        const float factor = 1.0f / HISTO_LENGTH;
+        const std::vector<MapPointT *> vpMPs = pKF->GetMapPointMatches();
+        // prologue (:1572-1612)
+        std::vector<int> qI;
+        std::vector<float> win;
+        std::vector<unsigned char> qDesc;
+        for (size_t i = 0, iend = vpMPs.size(); i < iend; i++) {
+            MapPointT *pMP = vpMPs[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+            const float xw[3] = {x3Dw.template at<float>(0, 0), x3Dw.template at<float>(1, 0), x3Dw.template at<float>(2, 0)};
+            float x3Dc[3];
+            mat_Rx_t(Rcw, xw, tcw, x3Dc);
+            const float xc = x3Dc[0], yc = x3Dc[1];
+            const float invzc = 1.0 / x3Dc[2];
+            const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+            const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+            if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+            if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+            const float PO[3] = {xw[0] - Ow[0], xw[1] - Ow[1], xw[2] - Ow[2]};
+            const float dist3D = norm3(PO);
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame);
+            const float radius = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+            qI.push_back((int)i);
+            const float wq[5] = {u, v, radius, (float)(nPredictedLevel - 1), (float)(nPredictedLevel + 1)};
+            win.insert(win.end(), wq, wq + 5);
+            const cv::Mat d = pMP->GetDescriptor();
+            qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_frame(CurrentFrame, win, qDesc, offs, cand, dist)) return 0;
+        // epilogue (:1614-1655)
+        for (size_t q = 0; q < qI.size(); q++) {
+            if (offs[q] == offs[q + 1]) continue;
+            const int i = qI[q];
+            int bestDist = 256, bestIdx2 = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t i2 = (size_t)cand[c];
+                if (CurrentFrame.mvpMapPoints[i2]) continue;
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx2 = (int)i2; }
+            }
+            if (bestDist <= ORBdist) {
+                CurrentFrame.mvpMapPoints[bestIdx2] = vpMPs[i];
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = pKF->mvKeysUn[i].angle - CurrentFrame.mvKeysUn[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2);
+                }
+            }
+        }
+        if (mbCheckOrientation) {
+            int ind1 = -1, ind2 = -1, ind3 = -1;
+            ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                if (i != ind1 && i != ind2 && i != ind3) {
+                    for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                        CurrentFrame.mvpMapPoints[rotHist[i][j]] = static_cast<MapPointT *>(NULL);
+                        nmatches--;
+                    }
+                }
+            }
+        }
+        return nmatches;
+    }
+
+    // Loop closing: project loop map points with a Sim3 (src/ORBmatcher.cc:305-422; caller src/LoopClosing.cc:399).
+    template <class KeyFrameT, class MapPointT>
+    int SearchByProjection(KeyFrameT *pKF, cv::Mat Scw, const std::vector<MapPointT *> &vpPoints, std::vector<MapPointT *> &vpMatched, int th)
+    {
+        float Rcw[9], tcw[3], Ow[3];
+        sim3_decompose(Scw, Rcw, tcw, Ow);
+        std::set<MapPointT *> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+        spAlreadyFound.erase(static_cast<MapPointT *>(NULL));
+        std::vector<int> qI, qLevel;
+        std::vector<float> qU, qV, win;
+        std::vector<unsigned char> qDesc;
+        for (int iMP = 0, iendMP = (int)vpPoints.size(); iMP < iendMP; iMP++) {
+            MapPointT *pMP = vpPoints[iMP];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            float u, v, dist3D;
+            if (!project_gated(pKF, Rcw, tcw, Ow, pMP, u, v, dist3D)) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+            const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+            push_query(pMP, iMP, nPredictedLevel, u, v, radius, qI, qLevel, qU, qV, win, qDesc);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_keyframe(pKF, win, qDesc, offs, cand, dist)) return 0;
+        int nmatches = 0;
+        for (size_t q = 0; q < qI.size(); q++) {
+            int bestDist = 256, bestIdx = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t idx = (size_t)cand[c];
+                if (vpMatched[idx]) continue;
+                const int kpLevel = pKF->mvKeysUn[idx].octave;
+                if (kpLevel < qLevel[q] - 1 || kpLevel > qLevel[q]) continue;
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+            }
+            if (bestDist <= TH_LOW) {
+                vpMatched[bestIdx] = vpPoints[qI[q]];
+                nmatches++;
+            }
+        }
+        return nmatches;
+    }
+
+    // Loop closing: fuse corrected loop map points into a keyframe (src/ORBmatcher.cc:1040-1164; caller
+    // src/LoopClosing.cc:663).
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT *pKF, cv::Mat Scw, const std::vector<MapPointT *> &vpPoints, float th, std::vector<MapPointT *> &vpReplacePoint)
+    {
+        float Rcw[9], tcw[3], Ow[3];
+        sim3_decompose(Scw, Rcw, tcw, Ow);
+        const std::set<MapPointT *> spAlreadyFound = pKF->GetMapPoints();
+        std::vector<int> qI, qLevel;
+        std::vector<float> qU, qV, win;
+        std::vector<unsigned char> qDesc;
+        const int nPoints = (int)vpPoints.size();
+        for (int iMP = 0; iMP < nPoints; iMP++) {
+            MapPointT *pMP = vpPoints[iMP];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            float u, v, dist3D;
+            if (!project_gated(pKF, Rcw, tcw, Ow, pMP, u, v, dist3D)) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+            const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+            push_query(pMP, iMP, nPredictedLevel, u, v, radius, qI, qLevel, qU, qV, win, qDesc);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_keyframe(pKF, win, qDesc, offs, cand, dist)) return 0;
+        int nFused = 0;
+        for (size_t q = 0; q < qI.size(); q++) {
+            // spAlreadyFound is a snapshot and isBad() is not changed inside this loop: no re-check needed
+            MapPointT *pMP = vpPoints[qI[q]];
+            int bestDist = INT_MAX_, bestIdx = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t idx = (size_t)cand[c];
+                const int kpLevel = pKF->mvKeysUn[idx].octave;
+                if (kpLevel < qLevel[q] - 1 || kpLevel > qLevel[q]) continue;
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+            }
+            if (bestDist <= TH_LOW) {
+                MapPointT *pMPinKF = pKF->GetMapPoint(bestIdx);
+                if (pMPinKF) {
+                    if (!pMPinKF->isBad()) vpReplacePoint[qI[q]] = pMPinKF;
+                } else {
+                    pMP->AddObservation(pKF, bestIdx);
+                    pKF->AddMapPoint(pMP, bestIdx);
+                }
+                nFused++;
+            }
+        }
+        return nFused;
+    }
+
+    // Loop closing: guided matching both ways under a Sim3 (src/ORBmatcher.cc:1166-1390; caller src/LoopClosing.cc:359).
+    template <class KeyFrameT, class MapPointT>
+    int SearchBySim3(KeyFrameT *pKF1, KeyFrameT *pKF2, std::vector<MapPointT *> &vpMatches12, const float &s12, const cv::Mat &R12,
+                     const cv::Mat &t12, const float th)
+    {
+        float R1w[9], t1w[3], R2w[9], t2w[3], sR12[9], sR21[9], t12f[3], t21[3];
+        {
+            const cv::Mat a = pKF1->GetRotation(), b = pKF1->GetTranslation(), c = pKF2->GetRotation(), d = pKF2->GetTranslation();
+            const float inv = (float)(1.0 / s12); // MatExpr scale factors reach convertTo as floats for 32F data
+            for (int r = 0; r < 3; r++) {
+                for (int k = 0; k < 3; k++) {
+                    R1w[3 * r + k] = a.template at<float>(r, k);
+                    R2w[3 * r + k] = c.template at<float>(r, k);
+                    sR12[3 * r + k] = R12.template at<float>(r, k) * s12;
+                    sR21[3 * r + k] = R12.template at<float>(k, r) * inv;
+                }
+                t1w[r] = b.template at<float>(r, 0);
+                t2w[r] = d.template at<float>(r, 0);
+                t12f[r] = t12.template at<float>(r, 0);
+            }
+            for (int r = 0; r < 3; r++)
+                t21[r] = -(float)((double)sR21[3 * r] * t12f[0] + (double)sR21[3 * r + 1] * t12f[1] + (double)sR21[3 * r + 2] * t12f[2]);
+        }
+        const std::vector<MapPointT *> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+        std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+        for (int i = 0; i < N1; i++) {
+            MapPointT *pMP = vpMatches12[i];
+            if (pMP) {
+                vbAlreadyMatched1[i] = true;
+                const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+            }
+        }
+        std::vector<int> vnMatch1(N1, -1), vnMatch2(N2, -1);
+        // the two directions are independent of each other: same helper, roles swapped
+        const float fx = pKF1->fx, fy = pKF1->fy, cx = pKF1->cx, cy = pKF1->cy;
+        if (!sim3_direction(pKF2, vpMapPoints1, vbAlreadyMatched1, R1w, t1w, sR21, t21, fx, fy, cx, cy, th, vnMatch1)) return 0;
+        if (!sim3_direction(pKF1, vpMapPoints2, vbAlreadyMatched2, R2w, t2w, sR12, t12f, fx, fy, cx, cy, th, vnMatch2)) return 0;
+        int nFound = 0;
+        for (int i1 = 0; i1 < N1; i1++) {
+            const int idx2 = vnMatch1[i1];
+            if (idx2 >= 0) {
+                const int idx1 = vnMatch2[idx2];
+                if (idx1 == i1) {
+                    vpMatches12[i1] = vpMapPoints2[idx2];
+                    nFound++;
+                }
+            }
+        }
+        return nFound;
+    }
+
     // Loop-closure matching between two keyframes (src/ORBmatcher.cc:568-702; caller src/LoopClosing.cc:323).
     template <class KeyFrameT, class MapPointT>
     int SearchByBoW(KeyFrameT *pKF1, KeyFrameT *pKF2, std::vector<MapPointT *> &vpMatches12)
@@ -687,6 +917,121 @@ protected:
     {
         for (int r = 0; r < 3; r++)
             y[r] = (float)((double)R[3 * r] * x[0] + (double)R[3 * r + 1] * x[1] + (double)R[3 * r + 2] * x[2] + (double)t[r]);
+    }
+
+    // Ow = -R^T * t (cv::gemm with alpha = -1: the double sum is negated, then narrowed)
+    static void camera_centre(const float *R, const float *t, float *Ow)
+    {
+        for (int i = 0; i < 3; i++) Ow[i] = -(float)((double)R[i] * t[0] + (double)R[3 + i] * t[1] + (double)R[6 + i] * t[2]);
+    }
+    // cv::norm of a 3-vector of floats: squares summed in double, sqrt in double, narrowed by the caller's float
+    static float norm3(const float *p)
+    {
+        return (float)std::sqrt((double)p[0] * p[0] + (double)p[1] * p[1] + (double)p[2] * p[2]);
+    }
+    // "Decompose Scw" (src/ORBmatcher.cc:313-318, 1049-1054): scw = |row 0| (Mat::dot accumulates in double),
+    // Rcw = sRcw / scw and tcw = t / scw (a MatExpr scale: each element times the FLOAT 1/scw), Ow = -Rcw^T tcw.
+    static void sim3_decompose(const cv::Mat &Scw, float *Rcw, float *tcw, float *Ow)
+    {
+        float sR[9], st[3];
+        pose_Rt(Scw, sR, st);
+        const float scw = (float)std::sqrt((double)sR[0] * sR[0] + (double)sR[1] * sR[1] + (double)sR[2] * sR[2]);
+        const float inv = (float)(1.0 / scw);
+        for (int i = 0; i < 9; i++) Rcw[i] = sR[i] * inv;
+        for (int i = 0; i < 3; i++) tcw[i] = st[i] * inv;
+        camera_centre(Rcw, tcw, Ow);
+    }
+    // The common gate of the Sim3 searches (src/ORBmatcher.cc:336-371, 1073-1108): positive depth, inside the image,
+    // distance inside the scale-invariance band, viewing angle below 60 degrees.
+    template <class KeyFrameT, class MapPointT>
+    static bool project_gated(KeyFrameT *pKF, const float *Rcw, const float *tcw, const float *Ow, MapPointT *pMP, float &u, float &v,
+                              float &dist3D)
+    {
+        const cv::Mat p3Dw = pMP->GetWorldPos();
+        const float pw[3] = {p3Dw.template at<float>(0, 0), p3Dw.template at<float>(1, 0), p3Dw.template at<float>(2, 0)};
+        float p3Dc[3];
+        mat_Rx_t(Rcw, pw, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) return false;
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        u = pKF->fx * x + pKF->cx;
+        v = pKF->fy * y + pKF->cy;
+        if (!pKF->IsInImage(u, v)) return false;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        const float PO[3] = {pw[0] - Ow[0], pw[1] - Ow[1], pw[2] - Ow[2]};
+        dist3D = norm3(PO);
+        if (dist3D < minDistance || dist3D > maxDistance) return false;
+        const cv::Mat Pn = pMP->GetNormal();
+        const double dot = (double)PO[0] * Pn.template at<float>(0, 0) + (double)PO[1] * Pn.template at<float>(1, 0) +
+                           (double)PO[2] * Pn.template at<float>(2, 0);
+        if (dot < 0.5 * dist3D) return false;
+        return true;
+    }
+    template <class MapPointT>
+    static void push_query(MapPointT *pMP, int i, int level, float u, float v, float radius, std::vector<int> &qI, std::vector<int> &qLevel,
+                           std::vector<float> &qU, std::vector<float> &qV, std::vector<float> &win, std::vector<unsigned char> &qDesc)
+    {
+        qI.push_back(i); qLevel.push_back(level); qU.push_back(u); qV.push_back(v);
+        const float wq[5] = {u, v, radius, -1.f, -1.f}; // KeyFrame::GetFeaturesInArea has no level filter (KeyFrame.cc:607)
+        win.insert(win.end(), wq, wq + 5);
+        const cv::Mat d = pMP->GetDescriptor();
+        qDesc.insert(qDesc.end(), d.ptr(), d.ptr() + 32);
+    }
+    // KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:607-647) for every window + distances; the grid is the keyframe's own
+    template <class KeyFrameT>
+    bool window_search_keyframe(KeyFrameT *pKF, const std::vector<float> &windows, const std::vector<unsigned char> &qDesc,
+                                std::vector<int> &offs, std::vector<int> &cand, std::vector<uint16_t> &dist)
+    {
+        return window_search(pKF->mvKeysUn, pKF->mDescriptors, pKF->mnMinX, pKF->mnMinY, pKF->mfGridElementWidthInv,
+                             pKF->mfGridElementHeightInv, pKF->mnGridCols, pKF->mnGridRows, windows, qDesc, offs, cand, dist);
+    }
+    // One direction of SearchBySim3 (src/ORBmatcher.cc:1212-1283 and :1286-1357): map points of pKFa, moved into the
+    // camera of pKFb by (sRba, tba) after (Raw, taw), matched inside pKFb's grid.  fx..cy are pKF1's in both directions.
+    template <class KeyFrameT, class MapPointT>
+    bool sim3_direction(KeyFrameT *pKFb, const std::vector<MapPointT *> &vpMapPointsA, const std::vector<bool> &vbAlreadyMatchedA,
+                        const float *Raw, const float *taw, const float *sRba, const float *tba, float fx, float fy, float cx, float cy,
+                        float th, std::vector<int> &vnMatchA)
+    {
+        std::vector<int> qI, qLevel;
+        std::vector<float> qU, qV, win;
+        std::vector<unsigned char> qDesc;
+        const int NA = (int)vpMapPointsA.size();
+        for (int i = 0; i < NA; i++) {
+            MapPointT *pMP = vpMapPointsA[i];
+            if (!pMP || vbAlreadyMatchedA[i]) continue;
+            if (pMP->isBad()) continue;
+            const cv::Mat p3Dw = pMP->GetWorldPos();
+            const float pw[3] = {p3Dw.template at<float>(0, 0), p3Dw.template at<float>(1, 0), p3Dw.template at<float>(2, 0)};
+            float pa[3], pb[3];
+            mat_Rx_t(Raw, pw, taw, pa);
+            mat_Rx_t(sRba, pa, tba, pb);
+            if (pb[2] < 0.0) continue;
+            const float invz = 1.0 / pb[2];
+            const float x = pb[0] * invz, y = pb[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKFb->IsInImage(u, v)) continue;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            const float dist3D = norm3(pb);
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, pKFb);
+            const float radius = th * pKFb->mvScaleFactors[nPredictedLevel];
+            push_query(pMP, i, nPredictedLevel, u, v, radius, qI, qLevel, qU, qV, win, qDesc);
+        }
+        std::vector<int> offs, cand;
+        std::vector<uint16_t> dist;
+        if (!window_search_keyframe(pKFb, win, qDesc, offs, cand, dist)) return false;
+        for (size_t q = 0; q < qI.size(); q++) {
+            int bestDist = INT_MAX_, bestIdx = -1;
+            for (int c = offs[q]; c < offs[q + 1]; c++) {
+                const size_t idx = (size_t)cand[c];
+                const int octave = pKFb->mvKeysUn[idx].octave;
+                if (octave < qLevel[q] - 1 || octave > qLevel[q]) continue;
+                const int d = dist[c];
+                if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+            }
+            if (bestDist <= TH_HIGH) vnMatchA[qI[q]] = bestIdx;
+        }
+        return true;
     }
 
     // Frame::GetFeaturesInArea for every window of a search + all candidate distances, in ONE device call

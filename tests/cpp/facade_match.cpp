@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <set>
 #include <type_traits>
 #include <vector>
 
@@ -32,7 +33,8 @@ struct MapPoint {
     float GetMaxDistanceInvariance() { return 1.2f * maxDist; }
     float GetMinDistanceInvariance() { return 0.8f * minDist; }
     cv::Mat GetNormal() { return normal.clone(); }
-    int PredictScale(const float &currentDist, KeyFrame *) {
+    int GetIndexInKeyFrame(KeyFrame *kf) { for (auto &o : observations) if (o.first == kf) return (int)o.second; return -1; }
+    template <class T> int PredictScale(const float &currentDist, T *) {
         const float ratio = maxDist / currentDist;
         int nScale = (int)std::ceil(std::log(ratio) / std::log(1.2f));
         if (nScale < 0) nScale = 0; else if (nScale >= 8) nScale = 7;
@@ -105,6 +107,7 @@ struct KeyFrame {
         return std::vector<size_t>(out.begin(), out.begin() + n);
     }
     std::vector<MapPoint *> GetMapPointMatches() { return mps; }
+    std::set<MapPoint *> GetMapPoints() { std::set<MapPoint *> r; for (MapPoint *m : mps) if (m) r.insert(m); return r; }
     MapPoint *GetMapPoint(const size_t &idx) { return mps[idx]; }
     cv::Mat GetCameraCenter() { return Ow.clone(); }
     cv::Mat GetRotation() { return Rcw.clone(); }
@@ -131,6 +134,94 @@ static void noisy_copy(const unsigned char *src, unsigned char *dst, int flips)
 {
     memcpy(dst, src, 32);
     for (int f = 0; f < flips; f++) { const unsigned b = rnd() % 256; dst[b >> 3] ^= (unsigned char)(1u << (b & 7)); }
+}
+
+// ---- small pose helpers of the checks below (CV_32F gemm semantics: double accumulation, one narrowing) -----------
+static void t_Rx_t(const float *R, const float *x, const float *t, float *y)
+{
+    for (int r = 0; r < 3; r++) y[r] = (float)((double)R[3 * r] * x[0] + (double)R[3 * r + 1] * x[1] + (double)R[3 * r + 2] * x[2] + (double)t[r]);
+}
+static void t_centre(const float *R, const float *t, float *O)
+{
+    for (int i = 0; i < 3; i++) O[i] = -(float)((double)R[i] * t[0] + (double)R[3 + i] * t[1] + (double)R[6 + i] * t[2]);
+}
+static float t_norm(const float *p) { return (float)std::sqrt((double)p[0] * p[0] + (double)p[1] * p[1] + (double)p[2] * p[2]); }
+static void rot_y(float ang, float *R)
+{
+    const float c = std::cos(ang), sn = std::sin(ang);
+    const float r[9] = {c, 0, sn, 0, 1, 0, -sn, 0, c};
+    memcpy(R, r, sizeof r);
+}
+static cv::Mat mat3(const float *R) { cv::Mat m; m.create(3, 3, CV_32F); for (int i = 0; i < 9; i++) m.at<float>(i / 3, i % 3) = R[i]; return m; }
+static cv::Mat vec3(const float *t) { cv::Mat m; m.create(3, 1, CV_32F); for (int i = 0; i < 3; i++) m.at<float>(i, 0) = t[i]; return m; }
+static cv::Mat mat4(const float *R, const float *t, float s)
+{
+    cv::Mat m; m.create(4, 4, CV_32F);
+    for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) m.at<float>(r, c) = r == c;
+    for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) m.at<float>(r, c) = s * R[3 * r + c]; m.at<float>(r, 3) = s * t[r]; }
+    return m;
+}
+// world point whose camera coordinates under (R, t) are pc:  R^T (pc - t)
+static void world_of(const float *R, const float *t, const float *pc, float *pw)
+{
+    for (int i = 0; i < 3; i++) pw[i] = (float)((double)R[i] * (pc[0] - t[0]) + (double)R[3 + i] * (pc[1] - t[1]) + (double)R[6 + i] * (pc[2] - t[2]));
+}
+static void keyframe_from(KeyFrame &K, const Frame &tmp)
+{
+    K.N = tmp.N; K.mps.assign(K.N, nullptr); K.mvuRight = tmp.mvuRight; K.mvKeysUn = tmp.mvKeys; K.mvScaleFactors = tmp.mvScaleFactors;
+    K.mvLevelSigma2.clear(); K.mvInvLevelSigma2.clear();
+    for (float f : K.mvScaleFactors) { K.mvLevelSigma2.push_back(f * f); K.mvInvLevelSigma2.push_back(1.0f / (f * f)); }
+    K.mDescriptors = tmp.mDescriptors.clone();
+    const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, z[3] = {0, 0, 0};
+    K.Rcw = mat3(I); K.tcw = vec3(z); K.Ow = vec3(z);
+}
+// a map point that lands near feature src of a keyframe-like target under camera pose (R, t), with a compatible scale band
+template <class T> static void point_near(MapPoint &m, const T &K, int src, const float *R, const float *t, float jitter)
+{
+    const float z = 3.f + 20.f * rndf();
+    const float u = K.mvKeysUn[src].pt.x + (rndf() - 0.5f) * jitter, v = K.mvKeysUn[src].pt.y + (rndf() - 0.5f) * jitter;
+    const float pc[3] = {(u - K.cx) * z / K.fx, (v - K.cy) * z / K.fy, rnd() % 40 ? z : -z};
+    float pw[3], O[3], PO[3];
+    world_of(R, t, pc, pw);
+    t_centre(R, t, O);
+    for (int i = 0; i < 3; i++) PO[i] = pw[i] - O[i];
+    const float nn = t_norm(PO);
+    m.pos = vec3(pw);
+    float nrm[3];
+    for (int i = 0; i < 3; i++) nrm[i] = (rnd() % 15 ? 1.f : -1.f) * PO[i] / nn;
+    m.normal = vec3(nrm);
+    m.maxDist = nn * std::pow(1.2f, (float)K.mvKeysUn[src].octave) * (0.9f + 0.2f * rndf());
+    m.minDist = m.maxDist / std::pow(1.2f, 7.f);
+    m.desc.create(1, 32, CV_8U);
+    noisy_copy(K.mDescriptors.ptr(src), m.desc.ptr(), rnd() % 70);
+    m.obs = 1 + rnd() % 5;
+    m.bad = rnd() % 30 == 0;
+}
+// reference gate of the Sim3 searches (src/ORBmatcher.cc:336-371), with the oracle-side arithmetic above
+static bool ref_gate(KeyFrame *pKF, const float *Rcw, const float *tcw, const float *Ow, MapPoint *pMP, float &u, float &v, float &dist)
+{
+    const float pw[3] = {pMP->pos.at<float>(0, 0), pMP->pos.at<float>(1, 0), pMP->pos.at<float>(2, 0)};
+    float pc[3];
+    t_Rx_t(Rcw, pw, tcw, pc);
+    if (pc[2] < 0.0f) return false;
+    const float invz = 1 / pc[2], x = pc[0] * invz, y = pc[1] * invz;
+    u = pKF->fx * x + pKF->cx; v = pKF->fy * y + pKF->cy;
+    if (!pKF->IsInImage(u, v)) return false;
+    const float PO[3] = {pw[0] - Ow[0], pw[1] - Ow[1], pw[2] - Ow[2]};
+    dist = t_norm(PO);
+    if (dist < pMP->GetMinDistanceInvariance() || dist > pMP->GetMaxDistanceInvariance()) return false;
+    const double dot = (double)PO[0] * pMP->normal.at<float>(0, 0) + (double)PO[1] * pMP->normal.at<float>(1, 0) + (double)PO[2] * pMP->normal.at<float>(2, 0);
+    return !(dot < 0.5 * dist);
+}
+static void ref_decompose(const cv::Mat &Scw, float *Rcw, float *tcw, float *Ow)
+{
+    float sR[9], st[3];
+    for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) sR[3 * r + c] = Scw.at<float>(r, c); st[r] = Scw.at<float>(r, 3); }
+    const float scw = (float)std::sqrt((double)sR[0] * sR[0] + (double)sR[1] * sR[1] + (double)sR[2] * sR[2]);
+    const float inv = (float)(1.0 / scw);
+    for (int i = 0; i < 9; i++) Rcw[i] = sR[i] * inv;
+    for (int i = 0; i < 3; i++) tcw[i] = st[i] * inv;
+    t_centre(Rcw, tcw, Ow);
 }
 
 // ---- the reference loops, straight, with the oracle's distance -------------------------------------------------
@@ -715,6 +806,262 @@ int main()
         }
         const bool same = ng == nr && got == want;
         printf("%s SearchByBoW(KeyFrame, KeyFrame): %d matches (reference loop %d)\n", same && ng > 200 ? "ok" : "FAIL", ng, nr);
+        fails += !(same && ng > 200);
+    }
+    // ---- M4: SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist)  (relocalisation)
+    for (int variant = 0; variant < 2; variant++) {
+        Frame C1, C2;
+        fill_frame(C1, 1500);
+        float R[9], t[3] = {0.08f, -0.02f, 0.15f};
+        rot_y(0.02f, R);
+        C1.mTcw = mat4(R, t, 1.f);
+        Frame tmpK;
+        fill_frame(tmpK, 1200);
+        KeyFrame K;
+        keyframe_from(K, tmpK);
+        std::vector<MapPoint> store(K.N);
+        std::set<MapPoint *> found;
+        for (int i = 0; i < K.N; i++) {
+            point_near(store[i], C1, rnd() % C1.N, R, t, 4.f);
+            if (rnd() % 6) K.mps[i] = &store[i];
+            if (rnd() % 12 == 0) found.insert(&store[i]);
+        }
+        for (int j = 0; j < C1.N; j++) if (rnd() % 4 == 0) C1.mvpMapPoints[j] = &store[rnd() % K.N]; // already claimed features
+        C2 = C1; C2.mDescriptors = C1.mDescriptors.clone();
+        const float th = variant ? 3.f : 10.f;
+        const int ORBdist = variant ? 64 : 100;
+        ORB_SLAM2::ORBmatcher matcher(0.9f, true);
+        const int ng = matcher.SearchByProjection(C1, &K, found, th, ORBdist);
+        int nr = 0;
+        {
+            float O[3];
+            t_centre(R, t, O);
+            std::vector<int> rotHist[30];
+            for (int i = 0; i < K.N; i++) {
+                MapPoint *pMP = K.mps[i];
+                if (!pMP || pMP->isBad() || found.count(pMP)) continue;
+                const float pw[3] = {pMP->pos.at<float>(0, 0), pMP->pos.at<float>(1, 0), pMP->pos.at<float>(2, 0)};
+                float pc[3];
+                t_Rx_t(R, pw, t, pc);
+                const float invzc = 1.0 / pc[2];
+                const float u = C2.fx * pc[0] * invzc + C2.cx, v = C2.fy * pc[1] * invzc + C2.cy;
+                if (u < C2.mnMinX || u > C2.mnMaxX || v < C2.mnMinY || v > C2.mnMaxY) continue;
+                const float PO[3] = {pw[0] - O[0], pw[1] - O[1], pw[2] - O[2]};
+                const float dist3D = t_norm(PO);
+                if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+                const int lvl = pMP->PredictScale(dist3D, &C2);
+                const std::vector<size_t> vi = C2.GetFeaturesInArea(u, v, th * C2.mvScaleFactors[lvl], lvl - 1, lvl + 1);
+                if (vi.empty()) continue;
+                int bestDist = 256, best = -1;
+                for (size_t i2 : vi) {
+                    if (C2.mvpMapPoints[i2]) continue;
+                    const int d = ref_descriptor_distance(pMP->desc.ptr(), C2.mDescriptors.ptr((int)i2));
+                    if (d < bestDist) { bestDist = d; best = (int)i2; }
+                }
+                if (bestDist <= ORBdist) {
+                    C2.mvpMapPoints[best] = pMP; nr++;
+                    float rot = K.mvKeysUn[i].angle - C2.mvKeysUn[best].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * (1.0f / 30));
+                    if (bin == 30) bin = 0;
+                    rotHist[bin].push_back(best);
+                }
+            }
+            int m1 = 0, m2 = 0, m3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                const int sz = (int)rotHist[i].size();
+                if (sz > m1) { m3 = m2; m2 = m1; m1 = sz; i3 = i2; i2 = i1; i1 = i; }
+                else if (sz > m2) { m3 = m2; m2 = sz; i3 = i2; i2 = i; }
+                else if (sz > m3) { m3 = sz; i3 = i; }
+            }
+            if (m2 < 0.1f * (float)m1) { i2 = -1; i3 = -1; } else if (m3 < 0.1f * (float)m1) i3 = -1;
+            for (int i = 0; i < 30; i++) {
+                if (i == i1 || i == i2 || i == i3) continue;
+                for (int j : rotHist[i]) { C2.mvpMapPoints[j] = nullptr; nr--; }
+            }
+        }
+        bool same = ng == nr;
+        for (int j = 0; j < C1.N; j++) same = same && C1.mvpMapPoints[j] == C2.mvpMapPoints[j];
+        printf("%s SearchByProjection(frame, keyframe, th=%g): %d matches (reference loop %d)\n", same && ng > 20 ? "ok" : "FAIL", th, ng, nr);
+        fails += !(same && ng > 20);
+    }
+    // ---- M5 + Fuse(Scw): Sim3 projection of loop map points into a keyframe
+    {
+        Frame tmp;
+        fill_frame(tmp, 1500);
+        KeyFrame KA, KB;
+        keyframe_from(KA, tmp); keyframe_from(KB, tmp);
+        float R[9], t[3] = {0.3f, 0.05f, -0.2f};
+        rot_y(-0.03f, R);
+        const cv::Mat Scw = mat4(R, t, 1.07f);
+        float Rd[9], td[3], Od[3];
+        ref_decompose(Scw, Rd, td, Od);
+        const int NP = 1400;
+        std::vector<MapPoint> storeA(NP + tmp.N), storeB;
+        for (int i = 0; i < NP; i++) point_near(storeA[i], KA, rnd() % tmp.N, Rd, td, 3.f);
+        for (int j = 0; j < tmp.N; j++) { storeA[NP + j].obs = 1 + rnd() % 5; storeA[NP + j].bad = rnd() % 20 == 0; }
+        storeB = storeA;
+        std::vector<MapPoint *> vpA, vpB;
+        for (int i = 0; i < NP; i++) { vpA.push_back(&storeA[i]); vpB.push_back(&storeB[i]); }
+        for (int i = 5; i < NP; i += 40) { vpA[i] = vpA[i - 3]; vpB[i] = vpB[i - 3]; }
+        // M5: vpMatched pre-filled for some features, some of the candidates among them
+        {
+            std::vector<MapPoint *> mA(tmp.N, nullptr), mB(tmp.N, nullptr);
+            for (int j = 0; j < tmp.N; j++) if (rnd() % 5 == 0) { const int k = rnd() % NP; mA[j] = &storeA[k]; mB[j] = &storeB[k]; }
+            ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+            const int ng = matcher.SearchByProjection(&KA, Scw, vpA, mA, 10);
+            int nr = 0;
+            std::set<MapPoint *> sp(mB.begin(), mB.end());
+            sp.erase(nullptr);
+            for (size_t i = 0; i < vpB.size(); i++) {
+                MapPoint *pMP = vpB[i];
+                if (pMP->isBad() || sp.count(pMP)) continue;
+                float u, v, dist;
+                if (!ref_gate(&KB, Rd, td, Od, pMP, u, v, dist)) continue;
+                const int lvl = pMP->PredictScale(dist, &KB);
+                const std::vector<size_t> vi = KB.GetFeaturesInArea(u, v, 10 * KB.mvScaleFactors[lvl]);
+                if (vi.empty()) continue;
+                int bestDist = 256, best = -1;
+                for (size_t idx : vi) {
+                    if (mB[idx]) continue;
+                    const int o = KB.mvKeysUn[idx].octave;
+                    if (o < lvl - 1 || o > lvl) continue;
+                    const int d = ref_descriptor_distance(pMP->desc.ptr(), KB.mDescriptors.ptr((int)idx));
+                    if (d < bestDist) { bestDist = d; best = (int)idx; }
+                }
+                if (bestDist <= 50) { mB[best] = pMP; nr++; }
+            }
+            bool same = ng == nr;
+            for (int j = 0; same && j < tmp.N; j++) same = (mA[j] ? mA[j] - storeA.data() : -1) == (mB[j] ? mB[j] - storeB.data() : -1);
+            printf("%s SearchByProjection(keyframe, Scw): %d matches (reference loop %d)\n", same && ng > 200 ? "ok" : "FAIL", ng, nr);
+            fails += !(same && ng > 200);
+        }
+        // Fuse(Scw)
+        {
+            for (int j = 0; j < tmp.N; j++) if (rnd() % 3 == 0) { KA.mps[j] = &storeA[NP + j]; KB.mps[j] = &storeB[NP + j]; }
+            for (int j = 0; j < tmp.N; j += 17) if (KA.mps[j]) { vpA.push_back(KA.mps[j]); vpB.push_back(KB.mps[j]); } // already in the keyframe
+            std::vector<MapPoint *> rA(vpA.size(), nullptr), rB(vpB.size(), nullptr);
+            ORB_SLAM2::ORBmatcher matcher(0.8f);
+            const int ng = matcher.Fuse(&KA, Scw, vpA, 4.f, rA);
+            int nr = 0;
+            const std::set<MapPoint *> sp = KB.GetMapPoints();
+            for (size_t i = 0; i < vpB.size(); i++) {
+                MapPoint *pMP = vpB[i];
+                if (pMP->isBad() || sp.count(pMP)) continue;
+                float u, v, dist;
+                if (!ref_gate(&KB, Rd, td, Od, pMP, u, v, dist)) continue;
+                const int lvl = pMP->PredictScale(dist, &KB);
+                const std::vector<size_t> vi = KB.GetFeaturesInArea(u, v, 4.f * KB.mvScaleFactors[lvl]);
+                if (vi.empty()) continue;
+                int bestDist = 0x7fffffff, best = -1;
+                for (size_t idx : vi) {
+                    const int o = KB.mvKeysUn[idx].octave;
+                    if (o < lvl - 1 || o > lvl) continue;
+                    const int d = ref_descriptor_distance(pMP->desc.ptr(), KB.mDescriptors.ptr((int)idx));
+                    if (d < bestDist) { bestDist = d; best = (int)idx; }
+                }
+                if (bestDist <= 50) {
+                    MapPoint *in = KB.GetMapPoint(best);
+                    if (in) { if (!in->isBad()) rB[i] = in; }
+                    else { pMP->AddObservation(&KB, best); KB.AddMapPoint(pMP, best); }
+                    nr++;
+                }
+            }
+            bool same = ng == nr;
+            for (int j = 0; same && j < tmp.N; j++) same = (KA.mps[j] ? KA.mps[j] - storeA.data() : -1) == (KB.mps[j] ? KB.mps[j] - storeB.data() : -1);
+            for (size_t i = 0; same && i < rA.size(); i++) same = (rA[i] ? rA[i] - storeA.data() : -1) == (rB[i] ? rB[i] - storeB.data() : -1);
+            for (size_t i = 0; same && i < storeA.size(); i++) same = storeA[i].obs == storeB[i].obs;
+            printf("%s Fuse(keyframe, Scw): %d fused (reference loop %d)\n", same && ng > 300 ? "ok" : "FAIL", ng, nr);
+            fails += !(same && ng > 300);
+        }
+    }
+    // ---- SearchBySim3
+    {
+        Frame tmp;
+        fill_frame(tmp, 1400);
+        KeyFrame K1, K2;
+        keyframe_from(K1, tmp); keyframe_from(K2, tmp);
+        const float s12 = 1.04f;
+        float R12[9], t12[3] = {0.25f, -0.03f, 0.1f};
+        rot_y(0.025f, R12);
+        // KF2's own world pose (KF1 = world): close to, not equal to, the inverse Sim3
+        float R2w[9], t2w[3] = {-0.24f, 0.03f, -0.09f};
+        rot_y(-0.024f, R2w);
+        K2.Rcw = mat3(R2w); K2.tcw = vec3(t2w);
+        float sR12[9], sR21[9], t21[3];
+        const float inv = (float)(1.0 / s12);
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) { sR12[3 * r + c] = R12[3 * r + c] * s12; sR21[3 * r + c] = R12[3 * c + r] * inv; }
+        for (int r = 0; r < 3; r++) t21[r] = -(float)((double)sR21[3 * r] * t12[0] + (double)sR21[3 * r + 1] * t12[1] + (double)sR21[3 * r + 2] * t12[2]);
+        std::vector<MapPoint> s1(tmp.N), s2(tmp.N);
+        const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, z0[3] = {0, 0, 0};
+        for (int i = 0; i < tmp.N; i++) {
+            // 3-D point seen by KF1 feature i; KF2 feature i is moved onto its Sim3 projection
+            const float z = 4.f + 20.f * rndf();
+            const float pc1[3] = {(K1.mvKeysUn[i].pt.x - K1.cx) * z / K1.fx, (K1.mvKeysUn[i].pt.y - K1.cy) * z / K1.fy, z};
+            float pc2[3];
+            t_Rx_t(sR21, pc1, t21, pc2);
+            const float u2 = K1.fx * pc2[0] / pc2[2] + K1.cx, v2 = K1.fy * pc2[1] / pc2[2] + K1.cy;
+            if (rnd() % 6 && u2 > 1 && u2 < 639 && v2 > 1 && v2 < 479) { K2.mvKeysUn[i].pt.x = u2 + (rndf() - 0.5f); K2.mvKeysUn[i].pt.y = v2 + (rndf() - 0.5f); }
+            noisy_copy(K1.mDescriptors.ptr(i), K2.mDescriptors.ptr(i), rnd() % 80);
+            MapPoint &a = s1[i], &b = s2[i];
+            a.pos = vec3(pc1); // world == camera 1
+            float pw2[3];
+            world_of(R2w, t2w, pc2, pw2); // KF2's map point: the world point that KF2's pose puts at pc2
+            b.pos = vec3(pw2);
+            a.maxDist = t_norm(pc2) * std::pow(1.2f, (float)K2.mvKeysUn[i].octave) * (0.93f + 0.14f * rndf());
+            b.maxDist = t_norm(pc1) * std::pow(1.2f, (float)K1.mvKeysUn[i].octave) * (0.93f + 0.14f * rndf());
+            a.minDist = a.maxDist / std::pow(1.2f, 7.f); b.minDist = b.maxDist / std::pow(1.2f, 7.f);
+            a.desc.create(1, 32, CV_8U); b.desc.create(1, 32, CV_8U);
+            memcpy(a.desc.ptr(), K1.mDescriptors.ptr(i), 32); memcpy(b.desc.ptr(), K2.mDescriptors.ptr(i), 32);
+            a.bad = rnd() % 30 == 0; b.bad = rnd() % 30 == 0;
+            if (rnd() % 8) K1.mps[i] = &a;
+            if (rnd() % 8) { K2.mps[i] = &b; b.observations.push_back({&K2, (size_t)i}); }
+        }
+        (void)I; (void)z0;
+        std::vector<MapPoint *> got(tmp.N, nullptr), want;
+        for (int i = 0; i < tmp.N; i += 9) if (K2.mps[i]) got[i] = K2.mps[i]; // matches already known (from SearchByBoW)
+        want = got;
+        ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+        const int ng = matcher.SearchBySim3(&K1, &K2, got, s12, mat3(R12), vec3(t12), 7.5f);
+        int nr = 0;
+        {
+            std::vector<bool> am1(tmp.N, false), am2(tmp.N, false);
+            for (int i = 0; i < tmp.N; i++) if (want[i]) { am1[i] = true; const int j = want[i]->GetIndexInKeyFrame(&K2); if (j >= 0 && j < tmp.N) am2[j] = true; }
+            std::vector<int> m1(tmp.N, -1), m2(tmp.N, -1);
+            for (int dir = 0; dir < 2; dir++) {
+                KeyFrame &Ka = dir ? K2 : K1, &Kb = dir ? K1 : K2;
+                const float *Raw = dir ? R2w : I, *taw = dir ? t2w : z0, *sR = dir ? sR12 : sR21, *tt = dir ? t12 : t21;
+                std::vector<bool> &am = dir ? am2 : am1;
+                std::vector<int> &mm = dir ? m2 : m1;
+                for (int i = 0; i < tmp.N; i++) {
+                    MapPoint *pMP = Ka.mps[i];
+                    if (!pMP || am[i] || pMP->isBad()) continue;
+                    const float pw[3] = {pMP->pos.at<float>(0, 0), pMP->pos.at<float>(1, 0), pMP->pos.at<float>(2, 0)};
+                    float pa[3], pb[3];
+                    t_Rx_t(Raw, pw, taw, pa);
+                    t_Rx_t(sR, pa, tt, pb);
+                    if (pb[2] < 0.0) continue;
+                    const float invz = 1.0 / pb[2], x = pb[0] * invz, y = pb[1] * invz, u = K1.fx * x + K1.cx, v = K1.fy * y + K1.cy;
+                    if (!Kb.IsInImage(u, v)) continue;
+                    const float dist3D = t_norm(pb);
+                    if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+                    const int lvl = pMP->PredictScale(dist3D, &Kb);
+                    const std::vector<size_t> vi = Kb.GetFeaturesInArea(u, v, 7.5f * Kb.mvScaleFactors[lvl]);
+                    if (vi.empty()) continue;
+                    int bestDist = 0x7fffffff, best = -1;
+                    for (size_t idx : vi) {
+                        const int o = Kb.mvKeysUn[idx].octave;
+                        if (o < lvl - 1 || o > lvl) continue;
+                        const int d = ref_descriptor_distance(pMP->desc.ptr(), Kb.mDescriptors.ptr((int)idx));
+                        if (d < bestDist) { bestDist = d; best = (int)idx; }
+                    }
+                    if (bestDist <= 100) mm[i] = best;
+                }
+            }
+            for (int i1 = 0; i1 < tmp.N; i1++) { const int i2 = m1[i1]; if (i2 >= 0 && m2[i2] == i1) { want[i1] = K2.mps[i2]; nr++; } }
+        }
+        const bool same = ng == nr && got == want;
+        printf("%s SearchBySim3: %d matches (reference loop %d)\n", same && ng > 200 ? "ok" : "FAIL", ng, nr);
         fails += !(same && ng > 200);
     }
     // ---- M1: static DescriptorDistance

@@ -89,4 +89,4 @@ def test_facade_matcher_templates_equal_reference_loops():
     exe = os.path.join(ROOT, "orb-slam2_b200", "facade_match.bin")
     assert os.path.exists(exe), "facade_match.bin not built: run __graft_entry__.build()"
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
-    assert r.returncode == 0 and r.stdout.count("ok ") == 11 and "FAIL" not in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and r.stdout.count("ok ") == 16 and "FAIL" not in r.stdout, r.stdout + r.stderr
