@@ -75,6 +75,12 @@ int orbb200_extract(orbb200_extractor *e, const uint8_t *img, int width, int hei
 int orbb200_extract_batch(orbb200_extractor *e, const uint8_t *const *imgs, int batch, int width, int height,
                           int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out);
 
+/* tuning of orbb200_extract_batch's copy/compute pipeline (no reference counterpart: the reference has no
+ * batching): the batch is cut into chunks of `chunk_images`; chunk c's upload, its kernels (rotating over
+ * `compute_streams` <= 4 CUDA streams) and chunk c-1's download overlap.  Defaults 32 and 4.  Results do
+ * not depend on either value. */
+int orbb200_extractor_set_pipeline(orbb200_extractor *e, int chunk_images, int compute_streams);
+
 /* device-resident variant: imgs_d holds `batch` images, image b at imgs_d + b*image_stride, rows `stride`
  * bytes apart; outputs are device buffers laid out as above.  Asynchronous on the handle's stream (see
  * orbb200_extractor_stream); no host synchronisation inside. */

@@ -192,10 +192,17 @@ int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes)
     for (int i = 0; i < 2; i++) {
         if (!e->evH2D[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evH2D[i], cudaEventDisableTiming));
         if (!e->evDone[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evDone[i], cudaEventDisableTiming));
+        if (!e->evStaged[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evStaged[i], cudaEventDisableTiming));
+    }
+    if (!e->evBegin) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evBegin, cudaEventDisableTiming));
+    for (int i = 0; i < orbb200_extractor::PIPE_STREAMS; i++) {
+        if (!e->workStream[i]) ORB_CUDA_OK(cudaStreamCreateWithFlags(&e->workStream[i], cudaStreamNonBlocking));
+        if (!e->evWork[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evWork[i], cudaEventDisableTiming));
     }
     if (e->stageBytes < stageBytes) {
         ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
         ORB_CUDA_OK(cudaStreamSynchronize(e->copyStream));
+        for (int i = 0; i < orbb200_extractor::PIPE_STREAMS; i++) ORB_CUDA_OK(cudaStreamSynchronize(e->workStream[i]));
         for (int i = 0; i < 2; i++) {
             if (e->d_stage[i]) { cudaFree(e->d_stage[i]); e->d_stage[i] = nullptr; }
             ORB_CUDA_OK(cudaMalloc((void **)&e->d_stage[i], stageBytes + 256));

@@ -19,7 +19,7 @@ TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist"
 EXPORTS = [
     "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
-    "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling",
+    "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
     "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_window_search", "orbb200_merge_top2",
@@ -59,6 +59,7 @@ def lib():
     L.orbb200_extractor_stream.restype = vp
     L.orbb200_extractor_sync.argtypes = [vp]
     L.orbb200_extractor_set_profiling.argtypes = [vp, ip]
+    L.orbb200_extractor_set_pipeline.argtypes = [vp, ip, ip]
     L.orbb200_extractor_stage_ms.argtypes = [vp, vp, ip]
     L.orbb200_extractor_stage_ms_sum.argtypes = [vp, vp, ip, vp]
     L.orbb200_extractor_last_launches.argtypes = [vp]
@@ -189,6 +190,9 @@ class ORBextractor:
 
     def sync(self):
         check(self.L.orbb200_extractor_sync(self.h))
+
+    def set_pipeline(self, chunk_images, compute_streams):
+        check(self.L.orbb200_extractor_set_pipeline(self.h, int(chunk_images), int(compute_streams)))
 
     def set_profiling(self, on):
         check(self.L.orbb200_extractor_set_profiling(self.h, int(on)))
