@@ -77,9 +77,13 @@ int orbb200_extract_batch(orbb200_extractor *e, const uint8_t *const *imgs, int 
 
 /* tuning of orbb200_extract_batch's copy/compute pipeline (no reference counterpart: the reference has no
  * batching): the batch is cut into chunks of `chunk_images`; chunk c's upload, its kernels (rotating over
- * `compute_streams` <= 4 CUDA streams) and chunk c-1's download overlap.  Defaults 32 and 4.  Results do
- * not depend on either value. */
-int orbb200_extractor_set_pipeline(orbb200_extractor *e, int chunk_images, int compute_streams);
+ * `compute_streams` <= 4 CUDA streams) and chunk c-1's download overlap.  Defaults 32 and 4.
+ * device_chunk_images > 0 makes orbb200_extract_batch_device cut its batch the same way (chunks joined back
+ * into the handle's stream before it returns, so the call stays stream-ordered for the caller); 0 = off, the
+ * default: resident batches fill the GPU kernel by kernel and chunking buys < 4 %.  With stage profiling on
+ * the device variant always runs unchunked on the handle's stream.
+ * Results do not depend on any of these values. */
+int orbb200_extractor_set_pipeline(orbb200_extractor *e, int chunk_images, int compute_streams, int device_chunk_images);
 
 /* device-resident variant: imgs_d holds `batch` images, image b at imgs_d + b*image_stride, rows `stride`
  * bytes apart; outputs are device buffers laid out as above.  Asynchronous on the handle's stream (see

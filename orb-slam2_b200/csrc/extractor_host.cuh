@@ -48,7 +48,7 @@ struct orbb200_extractor {
     cudaEvent_t evWork[PIPE_STREAMS] = {}, evBegin = nullptr;
     uint8_t *d_stage[2] = {nullptr, nullptr};
     size_t stageBytes = 0;
-    int pipeChunk = 32, pipeStreams = 4;
+    int pipeChunk = 32, pipeStreams = 4, devChunk = 0;
     // last call
     int lastBatch = 0, lastCap = 0;
     const uint8_t *lastL0 = nullptr;

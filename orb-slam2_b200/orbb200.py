@@ -59,7 +59,7 @@ def lib():
     L.orbb200_extractor_stream.restype = vp
     L.orbb200_extractor_sync.argtypes = [vp]
     L.orbb200_extractor_set_profiling.argtypes = [vp, ip]
-    L.orbb200_extractor_set_pipeline.argtypes = [vp, ip, ip]
+    L.orbb200_extractor_set_pipeline.argtypes = [vp, ip, ip, ip]
     L.orbb200_extractor_stage_ms.argtypes = [vp, vp, ip]
     L.orbb200_extractor_stage_ms_sum.argtypes = [vp, vp, ip, vp]
     L.orbb200_extractor_last_launches.argtypes = [vp]
@@ -191,8 +191,8 @@ class ORBextractor:
     def sync(self):
         check(self.L.orbb200_extractor_sync(self.h))
 
-    def set_pipeline(self, chunk_images, compute_streams):
-        check(self.L.orbb200_extractor_set_pipeline(self.h, int(chunk_images), int(compute_streams)))
+    def set_pipeline(self, chunk_images, compute_streams, device_chunk_images=0):
+        check(self.L.orbb200_extractor_set_pipeline(self.h, int(chunk_images), int(compute_streams), int(device_chunk_images)))
 
     def set_profiling(self, on):
         check(self.L.orbb200_extractor_set_profiling(self.h, int(on)))

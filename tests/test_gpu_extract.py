@@ -162,3 +162,46 @@ def test_device_api_equals_host_api(configs, layout):
         assert np.array_equal(desc_d[b, :n[b]].cpu().numpy(), desc_h[b, :n[b]])
     for l in range(nl):
         assert np.array_equal(ex2.pyramid_level(l, 1), ex.pyramid_level(l, 1)), l
+
+
+def test_pipeline_settings_do_not_change_results(configs):
+    """orbb200_extractor_set_pipeline only reschedules: any chunk size / stream count of the host pipeline, and the
+    optional chunking of the device variant (aligned and staged layouts), return byte-identical outputs, and the
+    stereo matcher that follows on the handle's stream sees all chunks."""
+    import torch
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    B = 10
+    imgs = np.stack([synth.textured_frame(w, h, 4100 + k) for k in range(B)])
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    ex.set_pipeline(B, 1, 0)
+    kps0, desc0, n0 = ex.extract_batch(imgs)
+    st0 = ex.stereo_match_batch(B // 2, 386.1448, 386.1448 / 718.856)
+    for chunk, ns in [(1, 4), (3, 2), (4, 3), (7, 4)]:
+        ex.set_pipeline(chunk, ns, 0)
+        kps, desc, n = ex.extract_batch(imgs)
+        assert np.array_equal(n, n0), (chunk, ns)
+        for b in range(B):
+            assert np.array_equal(kps[b, :n[b]].view(np.uint8), kps0[b, :n[b]].view(np.uint8)), (chunk, ns, b)
+            assert np.array_equal(desc[b, :n[b]], desc0[b, :n[b]]), (chunk, ns, b)
+        st = ex.stereo_match_batch(B // 2, 386.1448, 386.1448 / 718.856)
+        for a, b_ in zip(st, st0):
+            assert np.array_equal(a, b_), (chunk, ns)
+    cap = ex.cap
+    for pitch in (w, 1248):
+        raw = torch.zeros((B, h, pitch), dtype=torch.uint8, device="cuda")
+        raw[:, :, :w] = torch.from_numpy(imgs).cuda()
+        for chunk, ns in [(3, 4), (4, 2)]:
+            kps_d = torch.zeros((B, cap, 7), dtype=torch.float32, device="cuda")
+            desc_d = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+            n_d = torch.zeros(B, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            ex.set_pipeline(32, ns, chunk)
+            ex.extract_batch_device(raw.data_ptr(), B, w, h, pitch, pitch * h, kps_d.data_ptr(), desc_d.data_ptr(), cap, n_d.data_ptr())
+            uR, dep, nv = ex.stereo_match_batch(B // 2, 386.1448, 386.1448 / 718.856)  # ordered after every chunk
+            n = n_d.cpu().numpy()
+            assert np.array_equal(n, n0), (pitch, chunk, ns)
+            kd = kps_d.cpu().numpy().view(np.uint8).reshape(B, cap, 28)
+            for b in range(B):
+                assert np.array_equal(kd[b, :n[b]], kps0[b, :n[b]].view(np.uint8).reshape(-1, 28)), (pitch, chunk, ns, b)
+                assert np.array_equal(desc_d[b, :n[b]].cpu().numpy(), desc0[b, :n[b]]), (pitch, chunk, ns, b)
+            assert np.array_equal(uR, st0[0]) and np.array_equal(nv, st0[2]), (pitch, chunk, ns)
