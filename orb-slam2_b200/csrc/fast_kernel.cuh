@@ -9,19 +9,24 @@
 //   empty) yields the local maxima with S >= minTh -- one scoring pass serves both thresholds.
 //   ROI interiors tile [19, W-19) x [19, H-19) without overlap: every pixel is scored exactly once.
 //
-// sm_100a formulation (integer-ALU bound stage; ncu round 1: 245 thread instructions per pixel in the scalar form):
+// sm_100a formulation (integer-ALU / issue bound stage):
 //   * two pixels per thread in packed 16-bit lanes: VIMNMX3.S16x2 is a native instruction on sm_100a.
 //   * the arc minimum is translation invariant: max_arcs min9(v - ring) = v - min_arcs max9(ring), so the network
 //     runs on raw ring values (no 16 subtractions):  A = max_arcs min9(ring), B = min_arcs max9(ring),
 //     strength M = max(A - v, v - B); corner at t <=> M > t; score = M - 1.
 //     (The negation is applied once, outside the min/max chains: ptxas 12.9 drops a negation folded into
 //     VIMNMX3 -- see DESIGN.md.)
-//   * the ROI is staged in shared memory widened to 16 bits, twice: copy A holds pixel pairs starting at even
-//     positions, copy B the pairs starting at odd positions, so all 17 packed reads of a pixel pair are aligned
-//     conflict-free LDS.32 with no byte shuffling.
+//   * the ROI is staged in shared memory widened to 16 bits, twice: copy U holds the pixel pairs that start at even
+//     chunk columns, copy S the pairs that start at odd columns (both written with 128-bit stores), so all 17
+//     packed reads of a pixel pair are aligned conflict-free LDS.32 with no byte shuffling; which copy serves the
+//     even ring offsets depends on the parity of the cell's first interior column.
 //   * a warp-uniform quick test on the 4 compass ring pixels skips flat regions.
-//   * NMS flags become warp ballots; each warp owns a contiguous band of rows, so the reference's row-major order
-//     falls out of lane order + a 4-entry prefix -- no atomics, no block scan.
+//   * NMS is separable and stays packed: the scoring pass exchanges scores with the two neighbouring lanes
+//     (2 shuffles), keeps s' = s where s beats its horizontal neighbours and the 3-wide row maximum m3, and stores
+//     one word {s'0, s'1, m3_0, m3_1} per pixel pair; the second pass needs the words above and below only.
+//   * each warp owns a contiguous band of rows and appends its survivors to its own shared-memory list in lane
+//     order (= the reference's row-major order); after the block-wide iniTh/minTh vote the lists are copied to the
+//     cell's fixed slot -- no atomics, no block scan.
 #pragma once
 #include "extract_kernels.cuh"
 
@@ -30,27 +35,35 @@ namespace orbb200 {
 #ifdef ORBB200_EXTRACT_IMPL
 
 constexpr int FC_THREADS = 128, FC_WARPS = 4;
-constexpr int FC_SPW = 48;     // staged row pitch in 32-bit words per copy (96 halfwords)
-constexpr int FC_SCP = 64;     // score row pitch in bytes: interior <= 60 wide at column x + 2, zero border
-constexpr int FC_MAXROWS = 66; // hCell + 6 <= 66 (hCell < 60 because nRows = floor(height / 30))
-constexpr int FC_MAXG = 64;    // row groups per cell
+constexpr int FC_SPW = 48;      // staged row pitch in 32-bit words per copy (96 pixels = 6 chunks of 16)
+constexpr int FC_MAXROWS = 66;  // hCell + 6 <= 66 (hCell < 60 because nRows = floor(height / 30))
+constexpr int FC_LISTCAP = 256; // survivors per warp: <= ceil(15 / 2) * 30 strict local maxima in its <= 15 rows
 
 __host__ __device__ inline size_t fast_cells_smem(int rows)
 {
-    return (size_t)rows * FC_SPW * 4 * 2 + (size_t)(rows - 4) * FC_SCP + (size_t)FC_MAXG * 16 + 64;
+    // two widened copies + one score word per pixel pair (rows - 6 interior rows rounded up to a group, 2 border rows,
+    // 32 words per row at most) + the per-warp survivor lists
+    return (size_t)rows * FC_SPW * 4 * 2 + (size_t)(rows + 2) * 32 * 4 + (size_t)FC_WARPS * FC_LISTCAP * 4;
 }
 
 __device__ __forceinline__ unsigned int widen_lo(unsigned int w) { return __byte_perm(w, 0u, 0x4140); }
 __device__ __forceinline__ unsigned int widen_hi(unsigned int w) { return __byte_perm(w, 0u, 0x4342); }
+// 0xFFFF in each 16-bit half whose sign bit is set (prmt replicates the msb of bytes 1 and 3)
+__device__ __forceinline__ unsigned int neg_mask2(unsigned int w)
+{
+    unsigned int r;
+    asm("prmt.b32 %0, %1, 0, 0xBB99;" : "=r"(r) : "r"(w));
+    return r;
+}
 
-__global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant__ ExtractParams P, int rowsCap)
+__global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_constant__ ExtractParams P, int rowsCap)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
-    unsigned int *sA = reinterpret_cast<unsigned int *>(fsm);
-    unsigned int *sB = sA + rowsCap * FC_SPW;
-    uint8_t *sSc = reinterpret_cast<uint8_t *>(sB + rowsCap * FC_SPW);
-    uint4 *sBal = reinterpret_cast<uint4 *>(sSc + (rowsCap - 4) * FC_SCP);
-    int *sCnt = reinterpret_cast<int *>(sBal + FC_MAXG); // [FC_WARPS][2]
+    unsigned int *sU = reinterpret_cast<unsigned int *>(fsm);
+    unsigned int *sS = sU + rowsCap * FC_SPW;
+    unsigned int *sW = sS + rowsCap * FC_SPW;                 // [(rows + 2)][lanes per row], dense
+    unsigned int *sList = sW + (rowsCap + 2) * 32;            // [FC_WARPS][FC_LISTCAP]
+    __shared__ int sCnt[2 * FC_WARPS];
 
     const int c = blockIdx.x, b = blockIdx.y;
     int l = 0;
@@ -70,15 +83,14 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
     int pitch, valid;
     const uint8_t *img = level_ptr(P, g, l, b, pitch, valid);
     const int xb = iniX & ~15;
-    const int nbytes = ((maxX - xb) + 15) & ~15; // <= 96
-    const int o = (iniX + 3 - xb) & 1;           // staged index of image column gx: gx - xb + o
-    const int a0 = iniX + 3 - xb + o;            // staged index of the first interior column (even)
-    // ---- stage the ROI, widened to 16 bit, as copy A (pairs at even indices) and copy B (pairs at odd indices)
+    const int chunks = (((maxX - xb) + 15) & ~15) >> 4; // 3 .. 6
+    const int a = iniX + 3 - xb;                        // chunk column of the first interior pixel
+    // ---- stage the ROI, widened to 16 bit: U[k] = pixels (2k, 2k+1), S[k] = pixels (2k+1, 2k+2) of the row
     {
         const bool vec = ((((size_t)img) | (size_t)pitch) & 15) == 0;
-        const int chunks = nbytes >> 4;
+        const unsigned int magic = (65536u + chunks - 1) / chunks; // i / chunks for i < 400
         for (int i = tid; i < rh * chunks; i += FC_THREADS) {
-            const int r = i / chunks, ch = i - r * chunks, x = xb + (ch << 4);
+            const int r = (int)(((unsigned int)i * magic) >> 16), ch = i - r * chunks, x = xb + (ch << 4);
             const uint8_t *src = img + (size_t)(iniY + r) * pitch + x;
             unsigned int wd[5];
             if (vec && x + 16 <= valid) {
@@ -91,7 +103,7 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
                     if (x + k < g.w) wd[k >> 2] |= (unsigned int)__ldg(src + k) << ((k & 3) * 8);
             }
             wd[4] = (x + 16 < g.w) ? (unsigned int)__ldg(src + 16) : 0u;
-            unsigned int U[8], S[8]; // U[j] = pixels (2j, 2j+1), S[j] = pixels (2j+1, 2j+2) of the chunk
+            unsigned int U[8], S[8];
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 U[2 * j] = widen_lo(wd[j]);
@@ -100,42 +112,45 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
                 S[2 * j] = widen_lo(sh);
                 S[2 * j + 1] = widen_hi(sh);
             }
-            unsigned int *rowA = sA + r * FC_SPW + 8 * ch, *rowB = sB + r * FC_SPW + 8 * ch;
-            const int room = FC_SPW - 8 * ch - 1; // words 8ch+1 .. 8ch+8 must stay inside the row
-            if (o == 0) {
-                *reinterpret_cast<uint4 *>(rowA) = make_uint4(U[0], U[1], U[2], U[3]);
-                *reinterpret_cast<uint4 *>(rowA + 4) = make_uint4(U[4], U[5], U[6], U[7]);
-#pragma unroll
-                for (int j = 0; j < 8; j++)
-                    if (j < room) rowB[1 + j] = S[j];
-            } else {
-#pragma unroll
-                for (int j = 0; j < 8; j++)
-                    if (j < room) { rowA[1 + j] = S[j]; rowB[1 + j] = U[j]; }
-            }
+            uint4 *rowU = reinterpret_cast<uint4 *>(sU + r * FC_SPW + 8 * ch), *rowS = reinterpret_cast<uint4 *>(sS + r * FC_SPW + 8 * ch);
+            rowU[0] = make_uint4(U[0], U[1], U[2], U[3]);
+            rowU[1] = make_uint4(U[4], U[5], U[6], U[7]);
+            rowS[0] = make_uint4(S[0], S[1], S[2], S[3]);
+            rowS[1] = make_uint4(S[4], S[5], S[6], S[7]);
         }
     }
     const int iw = rw - 6, ih = rh - 6;
-    for (int i = tid; i < ((ih + 2) * FC_SCP) >> 2; i += FC_THREADS) reinterpret_cast<int *>(sSc)[i] = 0;
-    __syncthreads();
 
     // ---- thread <-> pixel pair; a warp covers 1, 2 or 4 interior rows; each warp owns a contiguous band of groups
     const int ppr = (iw + 1) >> 1;
     const int lprShift = ppr <= 8 ? 3 : (ppr <= 16 ? 4 : 5);
-    const int rpw = 32 >> lprShift;
+    const int lpr = 1 << lprShift, rpw = 32 >> lprShift;
     const int ngroups = (ih + rpw - 1) / rpw;
     const int gpw = (ngroups + FC_WARPS - 1) / FC_WARPS;
     const int g0 = wid * gpw, g1 = min(g0 + gpw, ngroups);
-    const int xl = lane & ((1 << lprShift) - 1), yl = lane >> lprShift;
+    const int xl = lane & (lpr - 1), yl = lane >> lprShift;
     const int x = 2 * xl;
+    // score words: row y of the interior is word row y + 1; word rows 0 and (ngroups * rpw) + 1 are the zero border
+    for (int i = tid; i < lpr; i += FC_THREADS) {
+        sW[i] = 0u;
+        sW[(ngroups * rpw + 1) * lpr + i] = 0u;
+    }
+    __syncthreads();
+
     const int minTh = P.minTh, iniTh = P.iniTh;
     const unsigned int thp1 = (unsigned int)(minTh + 1) * 0x10001u;
+    const unsigned int xmask = (xl < ppr) ? ((x + 1 < iw) ? 0xFFFFFFFFu : 0x0000FFFFu) : 0u;
+    // which copy serves the even ring offsets depends on the parity of the first interior column
+    const unsigned int *evenCopy = (a & 1) ? sS : sU, *oddCopy = (a & 1) ? sU : sS;
+    const int cofs = (a & 1) ? ((a - 1) >> 1) : (a >> 1);
+    const int oofs = (a & 1) ? cofs : cofs - 1;
 
     for (int gi = g0; gi < g1; gi++) {
         const int y = gi * rpw + yl;
         const bool act = (y < ih) && (xl < ppr);
-        const int wofs = (act ? (y + 3) * FC_SPW : 3 * FC_SPW) + ((a0 + (act ? x : 0)) >> 1);
-        const unsigned int *pa = sA + wofs, *pb = sB + wofs;
+        const int wrow = (act ? (y + 3) : 3) * FC_SPW + (act ? xl : 0);
+        const unsigned int *pa = evenCopy + wrow + cofs, *pb = oddCopy + wrow + oofs;
+        unsigned int *wout = sW + gi * 32 + lane + lpr;
         const unsigned int v = pa[0];
         unsigned int r[16];
         r[0] = pa[3 * FC_SPW];        // ( 0, 3)
@@ -148,7 +163,10 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
             const unsigned int td = __vmaxs2(__vmins2(r[0], r[8]), __vmins2(r[4], r[12]));
             const unsigned int q = __vmaxs2(__vsub2(tb, v), __vsub2(v, td)); // > minTh in a lane <=> a corner is possible
             const bool possible = act && ((__vsub2(q, thp1) & 0x80008000u) != 0x80008000u);
-            if (!__any_sync(0xffffffffu, possible)) continue;
+            if (!__any_sync(0xffffffffu, possible)) {
+                *wout = 0u;
+                continue;
+            }
         }
         r[1] = pb[3 * FC_SPW + 1];    // ( 1, 3)
         r[2] = pa[2 * FC_SPW + 1];    // ( 2, 2)
@@ -182,45 +200,53 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
         }
         A = __vmaxs2(A, mn9[15]);
         Bm = __vmins2(Bm, mx9[15]);
-        // strength per lane: darker ring v - B, brighter ring A - v
+        // strength per half: darker ring v - B, brighter ring A - v;  score = M - 1 where M > minTh, else 0
         const unsigned int M = __vmaxs2(__vsub2(A, v), __vsub2(v, Bm));
-        const int mlo = (int)(short)(M & 0xFFFFu), mhi = (int)M >> 16;
-        const int slo = mlo > minTh ? mlo - 1 : 0;
-        const int shi = (mhi > minTh && x + 1 < iw) ? mhi - 1 : 0;
-        if (act) *reinterpret_cast<unsigned short *>(sSc + (y + 1) * FC_SCP + x + 2) = (unsigned short)(slo | (shi << 8));
+        const unsigned int low = neg_mask2(__vsub2(M, thp1)); // M <= minTh
+        const unsigned int S = __vsub2(M, 0x00010001u) & ~low & (act ? xmask : 0u);
+        // horizontal part of the NMS: scores of the neighbouring pairs come from the neighbouring lanes
+        unsigned int SL = __shfl_up_sync(0xffffffffu, S, 1), SR = __shfl_down_sync(0xffffffffu, S, 1);
+        if (xl == 0) SL = 0u;
+        if (xl == lpr - 1) SR = 0u;
+        const unsigned int Sl = __byte_perm(SL, S, 0x5432); // (s(x-1), s(x))
+        const unsigned int Sr = __byte_perm(S, SR, 0x5432); // (s(x+1), s(x+2))
+        const unsigned int h = __vmaxs2(Sl, Sr);
+        const unsigned int m3 = __vmaxs2(h, S);
+        const unsigned int Sp = S & neg_mask2(__vsub2(h, S)); // s where s > both horizontal neighbours
+        *wout = __byte_perm(Sp, m3, 0x6420);                  // {s'0, s'1, m3_0, m3_1}
     }
     __syncthreads();
 
-    // ---- local maxima as ballots, per group; counts of the iniTh set and of the minTh set
-    int cntLm = 0, cntIni = 0;
+    // ---- vertical part of the NMS; survivors appended to the warp's list in lane order = row-major order
+    unsigned int *list = sList + wid * FC_LISTCAP;
+    const unsigned int lt = (1u << lane) - 1u;
+    const uint32_t base0 = (uint32_t)(cj * g.wCell + x + 3) | ((uint32_t)(ci * g.hCell + yl + 3) << 12);
+    int wcnt = 0;
     for (int gi = g0; gi < g1; gi++) {
-        const int y = gi * rpw + yl;
-        const bool act = (y < ih) && (xl < ppr);
-        const uint8_t *s = sSc + ((act ? y : 0) + 1) * FC_SCP + (act ? x : 0) + 2;
-        const unsigned int mid = act ? *reinterpret_cast<const unsigned short *>(s) : 0u;
-        bool lmLo = false, lmHi = false, inLo = false, inHi = false;
-        if (__any_sync(0xffffffffu, mid != 0u)) {
-            if (mid != 0u) {
-                const int v0 = mid & 0xFF, v1 = mid >> 8;
-                const int t0 = s[-FC_SCP - 1], t12 = *reinterpret_cast<const unsigned short *>(s - FC_SCP), t3 = s[-FC_SCP + 2];
-                const int b0 = s[FC_SCP - 1], b12 = *reinterpret_cast<const unsigned short *>(s + FC_SCP), b3 = s[FC_SCP + 2];
-                const int m0 = s[-1], m3 = s[2];
-                const int tm = max(t12 & 0xFF, t12 >> 8), bm = max(b12 & 0xFF, b12 >> 8);
-                const int n0 = __vimax3_s32(__vimax3_s32(t0, tm, b0), bm, max(m0, v1));
-                const int n1 = __vimax3_s32(__vimax3_s32(t3, tm, b3), bm, max(m3, v0));
-                lmLo = v0 > n0;
-                lmHi = v1 > n1;
-                inLo = lmLo && v0 >= iniTh;
-                inHi = lmHi && v1 >= iniTh;
-            }
+        const unsigned int *w = sW + gi * 32 + lane + lpr;
+        const unsigned int W = w[0];
+        if (!__any_sync(0xffffffffu, (W & 0xFFFFu) != 0u)) continue;
+        const unsigned int mx = __vmaxs2(widen_hi(w[-lpr]), widen_hi(w[lpr]));
+        const unsigned int s = widen_lo(W);
+        const unsigned int sk = s & neg_mask2(__vsub2(mx, s)); // s' where it also beats the rows above and below
+        const unsigned int lo = sk & 0xFFFFu, hi = sk >> 16;
+        const unsigned int bl = __ballot_sync(0xffffffffu, lo != 0u), bh = __ballot_sync(0xffffffffu, hi != 0u);
+        if (sk != 0u) {
+            int pos = wcnt + __popc(bl & lt) + __popc(bh & lt);
+            const uint32_t base = base0 + ((uint32_t)(gi * rpw) << 12);
+            if (lo != 0u && pos < FC_LISTCAP) list[pos++] = base | (lo << 24);
+            if (hi != 0u && pos < FC_LISTCAP) list[pos] = (base + 1u) | (hi << 24);
         }
-        const unsigned int bl = __ballot_sync(0xffffffffu, lmLo), bh = __ballot_sync(0xffffffffu, lmHi);
-        const unsigned int il = __ballot_sync(0xffffffffu, inLo), ihb = __ballot_sync(0xffffffffu, inHi);
-        if (lane == 0) sBal[gi] = make_uint4(bl, bh, il, ihb);
-        cntLm += __popc(bl) + __popc(bh);
-        cntIni += __popc(il) + __popc(ihb);
+        wcnt += __popc(bl) + __popc(bh);
     }
-    if (lane == 0) { sCnt[2 * wid] = cntLm; sCnt[2 * wid + 1] = cntIni; }
+    wcnt = min(wcnt, FC_LISTCAP);
+    __syncwarp();
+    int nIni = 0;
+    for (int i0 = 0; i0 < wcnt; i0 += 32) {
+        const int i = i0 + lane;
+        nIni += __popc(__ballot_sync(0xffffffffu, i < wcnt && (int)(list[i] >> 24) >= iniTh));
+    }
+    if (lane == 0) { sCnt[2 * wid] = wcnt; sCnt[2 * wid + 1] = nIni; }
     __syncthreads();
     int anyIni = 0, off = 0, total = 0;
 #pragma unroll
@@ -231,23 +257,20 @@ __global__ void __launch_bounds__(FC_THREADS) k_fast_cells(const __grid_constant
         if (w < wid) off += sCnt[2 * w + sel];
         total += sCnt[2 * w + sel];
     }
-    // ---- ordered write: groups in row order, lanes in column order, low pixel before high pixel
-    uint32_t *out = P.cand + (size_t)b * P.candStride + g.candOff + (size_t)cc * g.cellCap;
-    const unsigned int lt = (1u << lane) - 1u;
-    for (int gi = g0; gi < g1; gi++) {
-        const uint4 bal = sBal[gi];
-        const unsigned int ml = sel ? bal.z : bal.x, mh = sel ? bal.w : bal.y;
-        if ((ml | mh) == 0u) continue;
-        const int y = gi * rpw + yl;
-        const int mine = ((ml >> lane) & 1) + ((mh >> lane) & 1);
-        if (mine) {
-            int pos = off + __popc(ml & lt) + __popc(mh & lt);
-            const uint8_t *s = sSc + (y + 1) * FC_SCP + x + 2;
-            const uint32_t base = (uint32_t)(cj * g.wCell + x + 3) | ((uint32_t)(ci * g.hCell + y + 3) << 12);
-            if ((ml >> lane) & 1) out[pos++] = base | ((uint32_t)s[0] << 24);
-            if ((mh >> lane) & 1) out[pos] = (base + 1u) | ((uint32_t)s[1] << 24);
+    // ---- ordered copy of the selected set into the cell's fixed slot
+    uint32_t *out = P.cand + (size_t)b * P.candStride + g.candOff + (size_t)cc * g.cellCap + off;
+    if (!sel) {
+        for (int i = lane; i < wcnt; i += 32) out[i] = list[i];
+    } else {
+        int run = 0;
+        for (int i0 = 0; i0 < wcnt; i0 += 32) {
+            const int i = i0 + lane;
+            const uint32_t e = i < wcnt ? list[i] : 0u;
+            const bool ok = (int)(e >> 24) >= iniTh;
+            const unsigned int m = __ballot_sync(0xffffffffu, ok);
+            if (ok) out[run + __popc(m & lt)] = e;
+            run += __popc(m);
         }
-        off += __popc(ml) + __popc(mh);
     }
     if (tid == 0) *cellCount = total;
 }
