@@ -34,6 +34,7 @@ struct LevelGeom {
 struct ExtractParams {
     int nlevels, batch, iniTh, minTh;
     const LevelGeom *geom;
+    const uint4 *fastCells; // two uint4 per grid cell (all levels): ROI, image slot, output slot (orbb200_extract.cu)
     const uint8_t *l0; // level 0: caller's image (device API) or the level-0 slot of pyr (host API)
     size_t l0ImgStride;
     int l0Pitch, l0Valid;

@@ -23,6 +23,7 @@ struct orbb200_extractor {
     int fastRows = 7; // staged ROI rows of the largest cell (k_fast_cells dynamic shared memory)
     // device buffers
     orbb200::LevelGeom *d_geom = nullptr;
+    uint4 *d_fastCells = nullptr;
     int *d_umax = nullptr;
     int *d_rzXofs = nullptr, *d_rzYofs = nullptr;
     short2 *d_rzXa = nullptr, *d_rzYb = nullptr;

@@ -48,7 +48,12 @@ __host__ __device__ inline size_t fast_cells_smem(int rows)
 
 __device__ __forceinline__ unsigned int widen_lo(unsigned int w) { return __byte_perm(w, 0u, 0x4140); }
 __device__ __forceinline__ unsigned int widen_hi(unsigned int w) { return __byte_perm(w, 0u, 0x4342); }
-// 0xFFFF in each 16-bit half whose sign bit is set (prmt replicates the msb of bytes 1 and 3)
+// a - b per 16-bit half for halves in [0, 0x7FFF], BIASED by 0x8000: one plain 32-bit subtraction, no borrow can cross
+// the halves, bit 15 of a half is clear <=> a < b there; biased values order like unsigned halves (VIMNMX.U16x2).
+// (Deliberately not __vsub2: nvcc 12.9 splits its 16x2 negation constant wrongly in a peeled loop iteration --
+// the low half lost its +1 -- see DESIGN.md.)
+__device__ __forceinline__ unsigned int bsub2(unsigned int a, unsigned int b) { return (a | 0x80008000u) - b; }
+// 0xFFFF in each 16-bit half whose bit 15 is set (prmt replicates the msb of bytes 1 and 3)
 __device__ __forceinline__ unsigned int neg_mask2(unsigned int w)
 {
     unsigned int r;
@@ -66,29 +71,28 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
     __shared__ int sCnt[2 * FC_WARPS];
 
     const int c = blockIdx.x, b = blockIdx.y;
-    int l = 0;
-    while (l + 1 < P.nlevels && c >= P.geom[l + 1].cellBase) l++;
-    const LevelGeom g = P.geom[l];
-    const int cc = c - g.cellBase, ci = cc / g.nCols, cj = cc - ci * g.nCols;
-    const int maxBX = g.w - 16, maxBY = g.h - 16;
-    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
-    const int maxY = min(iniY + g.hCell + 6, maxBY), maxX = min(iniX + g.wCell + 6, maxBX);
-    const int rw = maxX - iniX, rh = maxY - iniY;
+    // per-cell record (built once per shape on the host): ROI, level, image slot, output slot
+    const uint4 r0 = ldg_nc_v4(P.fastCells + 2 * c), r1 = ldg_nc_v4(P.fastCells + 2 * c + 1);
+    const int rw = (int)(r0.y & 0xFFFFu), rh = (int)(r0.y >> 16);
     int *cellCount = P.cellCount + (size_t)b * P.totalCells + c;
-    if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || rw < 7 || rh < 7) { // skipped cell (:957-976) or empty interior
+    if (rw == 0) { // skipped cell (:957-976) or empty interior
         if (threadIdx.x == 0) *cellCount = 0;
         return;
     }
+    const int iniX = (int)(r0.x & 0xFFFFu), iniY = (int)(r0.x >> 16), maxX = iniX + rw;
+    const int gw = (int)(r0.w >> 16);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     int pitch, valid;
-    const uint8_t *img = level_ptr(P, g, l, b, pitch, valid);
+    const uint8_t *img;
+    if (r1.z == 0u) { pitch = P.l0Pitch; valid = P.l0Valid; img = P.l0 + (size_t)b * P.l0ImgStride; }
+    else { pitch = (int)(r0.w & 0xFFFFu); valid = pitch; img = P.pyr + (size_t)b * P.pyrStride + r0.z; }
     const int xb = iniX & ~15;
     const int chunks = (((maxX - xb) + 15) & ~15) >> 4; // 3 .. 6
     const int a = iniX + 3 - xb;                        // chunk column of the first interior pixel
     // ---- stage the ROI, widened to 16 bit: U[k] = pixels (2k, 2k+1), S[k] = pixels (2k+1, 2k+2) of the row
     {
         const bool vec = ((((size_t)img) | (size_t)pitch) & 15) == 0;
-        const unsigned int magic = (65536u + chunks - 1) / chunks; // i / chunks for i < 400
+        const unsigned int magic = r1.w; // ceil(65536 / chunks): i / chunks for i < 400
         for (int i = tid; i < rh * chunks; i += FC_THREADS) {
             const int r = (int)(((unsigned int)i * magic) >> 16), ch = i - r * chunks, x = xb + (ch << 4);
             const uint8_t *src = img + (size_t)(iniY + r) * pitch + x;
@@ -100,9 +104,9 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
                 wd[0] = wd[1] = wd[2] = wd[3] = 0;
 #pragma unroll
                 for (int k = 0; k < 16; k++)
-                    if (x + k < g.w) wd[k >> 2] |= (unsigned int)__ldg(src + k) << ((k & 3) * 8);
+                    if (x + k < gw) wd[k >> 2] |= (unsigned int)__ldg(src + k) << ((k & 3) * 8);
             }
-            wd[4] = (x + 16 < g.w) ? (unsigned int)__ldg(src + 16) : 0u;
+            wd[4] = (x + 16 < gw) ? (unsigned int)__ldg(src + 16) : 0u;
             unsigned int U[8], S[8];
 #pragma unroll
             for (int j = 0; j < 4; j++) {
@@ -138,19 +142,21 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
     __syncthreads();
 
     const int minTh = P.minTh, iniTh = P.iniTh;
-    const unsigned int thp1 = (unsigned int)(minTh + 1) * 0x10001u;
+    const unsigned int thp1 = (unsigned int)(minTh + 1) * 0x10001u, thm = (unsigned int)minTh * 0x10001u;
     const unsigned int xmask = (xl < ppr) ? ((x + 1 < iw) ? 0xFFFFFFFFu : 0x0000FFFFu) : 0u;
     // which copy serves the even ring offsets depends on the parity of the first interior column
     const unsigned int *evenCopy = (a & 1) ? sS : sU, *oddCopy = (a & 1) ? sU : sS;
     const int cofs = (a & 1) ? ((a - 1) >> 1) : (a >> 1);
     const int oofs = (a & 1) ? cofs : cofs - 1;
 
-    for (int gi = g0; gi < g1; gi++) {
-        const int y = gi * rpw + yl;
-        const bool act = (y < ih) && (xl < ppr);
-        const int wrow = (act ? (y + 3) : 3) * FC_SPW + (act ? xl : 0);
-        const unsigned int *pa = evenCopy + wrow + cofs, *pb = oddCopy + wrow + oofs;
-        unsigned int *wout = sW + gi * 32 + lane + lpr;
+    // running pointers: inactive lanes (columns past the interior, rows past it in the last group) read staged or
+    // stale shared memory that stays inside the block's allocation; their results are masked out below
+    const unsigned int *pa = evenCopy + (g0 * rpw + yl + 3) * FC_SPW + xl + cofs;
+    const unsigned int *pb = oddCopy + (g0 * rpw + yl + 3) * FC_SPW + xl + oofs;
+    unsigned int *wout = sW + g0 * 32 + lane + lpr;
+    for (int gi = g0; gi < g1; gi++, pa += rpw * FC_SPW, pb += rpw * FC_SPW, wout += 32) {
+        const unsigned int vmask = (gi * rpw + yl < ih) ? xmask : 0u;
+        const bool act = vmask != 0u;
         const unsigned int v = pa[0];
         unsigned int r[16];
         r[0] = pa[3 * FC_SPW];        // ( 0, 3)
@@ -161,8 +167,8 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
         {
             const unsigned int tb = __vmins2(__vmaxs2(r[0], r[8]), __vmaxs2(r[4], r[12]));
             const unsigned int td = __vmaxs2(__vmins2(r[0], r[8]), __vmins2(r[4], r[12]));
-            const unsigned int q = __vmaxs2(__vsub2(tb, v), __vsub2(v, td)); // > minTh in a lane <=> a corner is possible
-            const bool possible = act && ((__vsub2(q, thp1) & 0x80008000u) != 0x80008000u);
+            const unsigned int q = __vmaxu2(bsub2(tb, v), bsub2(v, td)); // biased; > minTh in a half <=> a corner is possible
+            const bool possible = act && (((q - thp1) & 0x80008000u) != 0u);
             if (!__any_sync(0xffffffffu, possible)) {
                 *wout = 0u;
                 continue;
@@ -200,10 +206,11 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
         }
         A = __vmaxs2(A, mn9[15]);
         Bm = __vmins2(Bm, mx9[15]);
-        // strength per half: darker ring v - B, brighter ring A - v;  score = M - 1 where M > minTh, else 0
-        const unsigned int M = __vmaxs2(__vsub2(A, v), __vsub2(v, Bm));
-        const unsigned int low = neg_mask2(__vsub2(M, thp1)); // M <= minTh
-        const unsigned int S = __vsub2(M, 0x00010001u) & ~low & (act ? xmask : 0u);
+        // strength per half: darker ring v - B, brighter ring A - v (biased by 0x8000, see bsub2);
+        // score = M - 1 where M > minTh, else 0
+        const unsigned int Mb = __vmaxu2(bsub2(A, v), bsub2(v, Bm));
+        const unsigned int cth = Mb - thp1;                                    // biased M - (minTh + 1): bit 15 set <=> M > minTh
+        const unsigned int S = (cth + thm) & neg_mask2(cth) & (vmask & 0x00FF00FFu); // biased M - 1, bias and losers masked off
         // horizontal part of the NMS: scores of the neighbouring pairs come from the neighbouring lanes
         unsigned int SL = __shfl_up_sync(0xffffffffu, S, 1), SR = __shfl_down_sync(0xffffffffu, S, 1);
         if (xl == 0) SL = 0u;
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
         const unsigned int Sr = __byte_perm(S, SR, 0x5432); // (s(x+1), s(x+2))
         const unsigned int h = __vmaxs2(Sl, Sr);
         const unsigned int m3 = __vmaxs2(h, S);
-        const unsigned int Sp = S & neg_mask2(__vsub2(h, S)); // s where s > both horizontal neighbours
+        const unsigned int Sp = S & ~neg_mask2(bsub2(h, S));  // s where s > both horizontal neighbours
         *wout = __byte_perm(Sp, m3, 0x6420);                  // {s'0, s'1, m3_0, m3_1}
     }
     __syncthreads();
@@ -220,15 +227,15 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
     // ---- vertical part of the NMS; survivors appended to the warp's list in lane order = row-major order
     unsigned int *list = sList + wid * FC_LISTCAP;
     const unsigned int lt = (1u << lane) - 1u;
-    const uint32_t base0 = (uint32_t)(cj * g.wCell + x + 3) | ((uint32_t)(ci * g.hCell + yl + 3) << 12);
+    const uint32_t base0 = r1.y + (uint32_t)x + ((uint32_t)yl << 12);
     int wcnt = 0;
-    for (int gi = g0; gi < g1; gi++) {
-        const unsigned int *w = sW + gi * 32 + lane + lpr;
+    const unsigned int *w = sW + g0 * 32 + lane + lpr;
+    for (int gi = g0; gi < g1; gi++, w += 32) {
         const unsigned int W = w[0];
         if (!__any_sync(0xffffffffu, (W & 0xFFFFu) != 0u)) continue;
         const unsigned int mx = __vmaxs2(widen_hi(w[-lpr]), widen_hi(w[lpr]));
         const unsigned int s = widen_lo(W);
-        const unsigned int sk = s & neg_mask2(__vsub2(mx, s)); // s' where it also beats the rows above and below
+        const unsigned int sk = s & ~neg_mask2(bsub2(mx, s)); // s' where it also beats the rows above and below
         const unsigned int lo = sk & 0xFFFFu, hi = sk >> 16;
         const unsigned int bl = __ballot_sync(0xffffffffu, lo != 0u), bh = __ballot_sync(0xffffffffu, hi != 0u);
         if (sk != 0u) {
@@ -258,7 +265,7 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
         total += sCnt[2 * w + sel];
     }
     // ---- ordered copy of the selected set into the cell's fixed slot
-    uint32_t *out = P.cand + (size_t)b * P.candStride + g.candOff + (size_t)cc * g.cellCap + off;
+    uint32_t *out = P.cand + (size_t)b * P.candStride + r1.x + off;
     if (!sel) {
         for (int i = lane; i < wcnt; i += 32) out[i] = list[i];
     } else {

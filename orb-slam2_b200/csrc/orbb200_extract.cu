@@ -148,6 +148,30 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
             if ((size_t)maxBytes * maxRows > 160 * 1024) { set_error("scale factor too large for the resize tile"); return ORBB200_ERR_ARG; }
         }
         if (dev_alloc(&e->d_geom, L)) return ORBB200_ERR_CUDA;
+        {
+            // per-cell records of k_fast_cells: the ROI of src/ORBextractor.cc:953-985 for every cell of every level,
+            // worked out once per shape so that a block starts with one 32-byte load instead of a level search
+            std::vector<uint4> cells((size_t)2 * std::max(e->totalCells, 1), make_uint4(0, 0, 0, 0));
+            for (int l = 0; l < L; l++) {
+                const LevelGeom &g = e->geom[l];
+                const int maxBX = g.w - 16, maxBY = g.h - 16;
+                for (int cc = 0; cc < g.nCells; cc++) {
+                    const int ci = cc / g.nCols, cj = cc - ci * g.nCols;
+                    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
+                    const int maxY = std::min(iniY + g.hCell + 6, maxBY), maxX = std::min(iniX + g.wCell + 6, maxBX);
+                    int rw = maxX - iniX, rh = maxY - iniY;
+                    if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || rw < 7 || rh < 7) rw = rh = 0; // skipped cell (:957-976)
+                    const int chunks = rw ? ((((maxX - (iniX & ~15)) + 15) & ~15) >> 4) : 1;
+                    uint4 &r0 = cells[(size_t)2 * (g.cellBase + cc)], &r1 = cells[(size_t)2 * (g.cellBase + cc) + 1];
+                    r0 = make_uint4((unsigned)iniX | ((unsigned)iniY << 16), (unsigned)rw | ((unsigned)rh << 16), g.imgOff,
+                                    (unsigned)g.pitch | ((unsigned)g.w << 16));
+                    r1 = make_uint4(g.candOff + (unsigned)cc * g.cellCap, (unsigned)(cj * g.wCell + 3) | ((unsigned)(ci * g.hCell + 3) << 12),
+                                    (unsigned)l, (65536u + chunks - 1) / chunks);
+                }
+            }
+            if (dev_alloc(&e->d_fastCells, cells.size())) return ORBB200_ERR_CUDA;
+            ORB_CUDA_OK(cudaMemcpy(e->d_fastCells, cells.data(), sizeof(uint4) * cells.size(), cudaMemcpyHostToDevice));
+        }
         if (dev_alloc(&e->d_rzXofs, coefOff) || dev_alloc(&e->d_rzYofs, coefOff) || dev_alloc(&e->d_rzXa, coefOff) ||
             dev_alloc(&e->d_rzYb, coefOff))
             return ORBB200_ERR_CUDA;
