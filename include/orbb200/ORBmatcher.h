@@ -562,7 +562,7 @@ public:
     }
 
     // Relocalisation: project the map points of a candidate keyframe into the current frame
-    // (src/ORBmatcher.cc:1555-1685; caller src/Tracking.cc:1504, 1518).
+    // (src/ORBmatcher.cc:1555-1685; callers src/Tracking.cc:1763, 1777).
     template <class FrameT, class KeyFrameT, class SetT>
     int SearchByProjection(FrameT &CurrentFrame, KeyFrameT *pKF, const SetT &sAlreadyFound, const float th, const int ORBdist)
     {
@@ -645,7 +645,7 @@ public:
         return nmatches;
     }
 
-    // Loop closing: project loop map points with a Sim3 (src/ORBmatcher.cc:305-422; caller src/LoopClosing.cc:399).
+    // Loop closing: project loop map points with a Sim3 (src/ORBmatcher.cc:305-422; caller src/LoopClosing.cc:464).
     template <class KeyFrameT, class MapPointT>
     int SearchByProjection(KeyFrameT *pKF, cv::Mat Scw, const std::vector<MapPointT *> &vpPoints, std::vector<MapPointT *> &vpMatched, int th)
     {
@@ -688,7 +688,7 @@ public:
     }
 
     // Loop closing: fuse corrected loop map points into a keyframe (src/ORBmatcher.cc:1040-1164; caller
-    // src/LoopClosing.cc:663).
+    // src/LoopClosing.cc:745).
     template <class KeyFrameT, class MapPointT>
     int Fuse(KeyFrameT *pKF, cv::Mat Scw, const std::vector<MapPointT *> &vpPoints, float th, std::vector<MapPointT *> &vpReplacePoint)
     {
@@ -737,7 +737,7 @@ public:
         return nFused;
     }
 
-    // Loop closing: guided matching both ways under a Sim3 (src/ORBmatcher.cc:1166-1390; caller src/LoopClosing.cc:359).
+    // Loop closing: guided matching both ways under a Sim3 (src/ORBmatcher.cc:1166-1390; caller src/LoopClosing.cc:391).
     template <class KeyFrameT, class MapPointT>
     int SearchBySim3(KeyFrameT *pKF1, KeyFrameT *pKF2, std::vector<MapPointT *> &vpMatches12, const float &s12, const cv::Mat &R12,
                      const cv::Mat &t12, const float th)
