@@ -1,13 +1,19 @@
 // describe_kernel.cuh -- E6 + E8 + E9: IC_Angle orientation (src/ORBextractor.cc:83-111), 256-bit rBRIEF
-// (:116-157) and output assembly (:1288-1338) in one kernel, one warp per selected keypoint.
+// (:116-157) and output assembly (:1288-1338) in one kernel; a warp walks DS_KPW selected keypoints.
 //
 // Round-1 ncu of the first version: 1430 warp instructions per keypoint, long-scoreboard bound (16 scattered byte
-// gathers per lane = 512 L1 sectors per keypoint), XU pipe busy with I2F/F2I.  This version:
-//   * the 37-row blurred patch of the keypoint is staged in shared memory with 16-byte row loads (74 sectors), and
-//     the 512 samples become LDS.U8;
+// gathers per lane = 512 L1 sectors per keypoint), XU pipe busy with I2F/F2I; second version (smem-staged blurred
+// patch): 1000 instructions, half of them the 31 predicated byte loads per lane of the orientation disc and a
+// per-keypoint prologue (pattern fill, level search, geometry load).  This version:
+//   * block prologue once per 32 keypoints: pattern to smem, per-level tables held one level per lane (level of a slot
+//     = one ballot + popc, its geometry = shuffles), disc masks built in registers;
+//   * BOTH patches of a keypoint are staged in shared memory with 16-byte row loads (blurred 37 x 64, un-blurred
+//     31 x 48): 8 loads per lane in flight instead of 31 + 16 dependent byte gathers;
+//   * orientation: lane <-> disc ROW; the 31 bytes of the row are 3 conflict-free LDS.128, aligned by one funnel
+//     shift per word, masked to the disc, and reduced with DP4A (row sum, and column-weighted sum for m10) --
+//     16 DP4A replace 31 x (load, predicate, 2 multiply-adds);
 //   * the pattern lives in shared memory as floats, transposed so that the lanes' float4 reads are conflict free;
 //   * cvRound = add 1.5*2^23 and take the mantissa (round-half-even, exact for |x| < 2^22) instead of F2I;
-//   * the orientation disc is fully unrolled with the (fixed) umax table as immediates, all 31 loads in flight;
 //   * cos/sin of the angle come from one double-precision fdlibm-style sincos on [0, 2*pi], rounded to float
 //     (glibc's cosf/sinf are correctly rounded).
 #pragma once
@@ -15,8 +21,9 @@
 
 namespace orbb200 {
 
-constexpr int DS_WARPS = 8;
+constexpr int DS_WARPS = 8, DS_KPW = 4;      // warps per block, keypoint slots per warp
 constexpr int DS_PROWS = 37, DS_PPITCH = 64; // staged blurred patch: rows y-18..y+18, 64 bytes from (x-18) & ~15
+constexpr int DS_RROWS = 32, DS_RPITCH = 48; // staged un-blurred patch: rows y-15..y+15 (+1 pad), 48 bytes from (x-15) & ~15
 
 __constant__ signed char c_pattern[256][4] = {
 #include "orb_pattern.inc"
@@ -77,127 +84,184 @@ __device__ __forceinline__ int cv_round_magic(float v)
     return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
 }
 
+__device__ __forceinline__ int dp4a_us(unsigned int a, unsigned int b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// m10 / m01 of the radius-15 disc from the staged un-blurred patch; lane <-> row v = lane - 15.
+// KW = word offset of the row's first disc byte inside the lane's 12 staged words (warp-uniform, 0..3).
+template <int KW> __device__ __forceinline__ void disc_row_sums(const uint4 &q0, const uint4 &q1, const uint4 &q2, unsigned int sb,
+                                                                const unsigned int (&mk)[8], int &s, int &t)
+{
+    const unsigned int w[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
+    s = 0; t = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const unsigned int lo = w[KW + j], hi = (KW + j + 1 < 12) ? w[KW + j + 1] : 0u;
+        const unsigned int px = __funnelshift_r(lo, hi, sb) & mk[j];
+        // byte k of the row is column u = k - 15: weights (4j-15, 4j-14, 4j-13, 4j-12) as signed bytes
+        const unsigned int wt = (unsigned int)((4 * j - 15) & 0xFF) | ((unsigned int)((4 * j - 14) & 0xFF) << 8) |
+                                ((unsigned int)((4 * j - 13) & 0xFF) << 16) | ((unsigned int)((4 * j - 12) & 0xFF) << 24);
+        s = (int)__dp4a(px, 0x01010101u, (unsigned int)s);
+        t = dp4a_us(px, wt, t);
+    }
+}
+
 __global__ void __launch_bounds__(DS_WARPS * 32) k_orient_describe(const __grid_constant__ ExtractParams P)
 {
     __shared__ __align__(16) float4 sPat[8 * 32];                               // [bit k of the byte][lane]
     __shared__ __align__(16) uint8_t sPatch[DS_WARPS][DS_PROWS * DS_PPITCH];
+    __shared__ __align__(16) uint8_t sRaw[DS_WARPS][DS_RROWS * DS_RPITCH];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         // pattern pair i belongs to descriptor byte i / 8 (= lane), bit i % 8
         sPat[(i & 7) * 32 + (i >> 3)] = make_float4((float)c_pattern[i][0], (float)c_pattern[i][1], (float)c_pattern[i][2], (float)c_pattern[i][3]);
     }
-    __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int slot = blockIdx.x * DS_WARPS + wid, b = blockIdx.y;
-    // per-level counts of this image -> output offset of each level (levels concatenated 0..L-1, :1302-1337)
-    const int cnt = lane < P.nlevels ? P.lvlCount[(size_t)b * P.nlevels + lane] : 0;
-    int inc = cnt;
+    const int b = blockIdx.y;
+    // ---- per-level tables, one level per lane: node slot range, keypoint count, output offset, image slot, scale
+    int tNodeOff = 0x7fffffff, tCnt = 0, tPitch = 0;
+    unsigned int tImgOff = 0;
+    float tScale = 1.f, tPatch = 31.f;
+    if (lane < P.nlevels) {
+        const LevelGeom *g = P.geom + lane;
+        tNodeOff = g->nodeOff; tPitch = g->pitch; tImgOff = g->imgOff; tScale = g->scale; tPatch = g->patch;
+        tCnt = P.lvlCount[(size_t)b * P.nlevels + lane];
+    }
+    int inc = tCnt; // levels concatenated 0..L-1 in the output (:1302-1337)
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += t;
     }
-    const int total = __shfl_sync(0xffffffffu, inc, 31);
-    if (blockIdx.x == 0 && wid == 0 && lane == 0) P.nOut[b] = total;
-    if (slot >= P.nodeTotal) return;
-    int l = 0;
-    while (l + 1 < P.nlevels && slot >= P.geom[l + 1].nodeOff) l++;
-    const LevelGeom g = P.geom[l];
-    const int pos = slot - g.nodeOff;
-    const int cntL = __shfl_sync(0xffffffffu, cnt, l), offL = __shfl_sync(0xffffffffu, inc - cnt, l);
-    if (pos >= cntL) return;
-    const int outIdx = offL + pos;
-    if (outIdx >= P.cap) return;
-    const uint32_t packed = P.lvlKp[(size_t)b * P.nodeTotal + slot];
-    const int x = (int)(packed & 0xFFF) + 16, y = (int)((packed >> 12) & 0xFFF) + 16;
-    const int resp = (int)(packed >> 24);
-
-    // ---- stage the blurred 37 x 37 patch (rows y-18..y+18, 16-byte chunks from (x-18) & ~15): issued first so that
-    //      its latency overlaps the orientation below
-    const uint8_t *bl = P.blur + (size_t)b * P.pyrStride + g.imgOff;
-    const int px0 = (x - 18) & ~15;
-    uint8_t *patch = sPatch[wid];
+    const int tOutOff = inc - tCnt;
+    if (blockIdx.x == 0 && wid == 0 && lane == 31) P.nOut[b] = inc;
+    // ---- disc mask of this lane's row v = lane - 15: bytes k with |k - 15| <= umax[|v|]
+    //      (umax of src/ORBextractor.cc:510-533 for HALF_PATCH_SIZE = 15; orbb200_compute_level_tables reproduces it)
+    unsigned int mk[8];
     {
-        uint4 v[5];
+        constexpr unsigned long long UMP = 0x3689ABCDDEEEFFFFull; // umax[0..15] = 15 15 15 15 14 14 14 13 13 12 11 10 9 8 6 3, 4 bits each
+        const int av = abs(lane - 15);
+        const int um = av < 16 ? (int)((UMP >> (4 * av)) & 15) : -1;
+        const unsigned int bits = um >= 0 ? (((1u << (2 * um + 1)) - 1u) << (15 - um)) : 0u;
 #pragma unroll
-        for (int i = 0; i < 5; i++) {
-            const int idx = lane + 32 * i; // chunk index: row = idx / 4, chunk = idx % 4
-            const int r = idx >> 2, ch = idx & 3;
-            const int gx = px0 + (ch << 4);
-            v[i] = make_uint4(0, 0, 0, 0);
-            if (idx < DS_PROWS * 4 && gx < g.pitch) v[i] = ldg_nc_v4(bl + (size_t)(y - 18 + r) * g.pitch + gx);
-        }
-#pragma unroll
-        for (int i = 0; i < 5; i++) {
-            const int idx = lane + 32 * i;
-            if (idx < DS_PROWS * 4) *reinterpret_cast<uint4 *>(patch + (idx >> 2) * DS_PPITCH + ((idx & 3) << 4)) = v[i];
-        }
+        for (int j = 0; j < 8; j++) mk[j] = ((((bits >> (4 * j)) & 15u) * 0x00204081u) & 0x01010101u) * 0xFFu;
     }
+    __syncthreads();
 
-    // ---- E6: intensity-centroid moments over the radius-15 disc of the UN-blurred level; lane <-> column u
-    int pitch, valid;
-    const uint8_t *img = level_ptr(P, g, l, b, pitch, valid);
-    int m10 = 0, m01 = 0;
-    {
-        // umax of src/ORBextractor.cc:510-533 for HALF_PATCH_SIZE = 15 (orbb200_compute_level_tables reproduces it)
-        constexpr int UM[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-        const int u = lane - 15;
-        const int au = abs(u);
-        const uint8_t *c = img + (size_t)y * pitch + x + u;
-        int vals[31];
-#pragma unroll
-        for (int v = -15; v <= 15; v++) {
-            const int av = v < 0 ? -v : v;
-            vals[v + 15] = (lane < 31 && au <= UM[av]) ? (int)__ldg(c + v * pitch) : 0;
-        }
-        int s = 0;
-#pragma unroll
-        for (int v = -15; v <= 15; v++) {
-            s += vals[v + 15];
-            m01 += v * vals[v + 15];
-        }
-        m10 = u * s;
-    }
-    m10 = warp_sum(m10);
-    m01 = warp_sum(m01);
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    uint8_t *patch = sPatch[wid], *raw = sRaw[wid];
+    const int slot0 = (blockIdx.x * DS_WARPS + wid) * DS_KPW;
+    for (int kpi = 0; kpi < DS_KPW; kpi++) {
+        const int slot = slot0 + kpi;
+        if (slot >= P.nodeTotal) break;
+        const int l = __popc(__ballot_sync(0xffffffffu, slot >= tNodeOff)) - 1; // nodeOff ascends with the level
+        const int pos = slot - __shfl_sync(0xffffffffu, tNodeOff, l);
+        if (pos >= __shfl_sync(0xffffffffu, tCnt, l)) continue;
+        const int outIdx = __shfl_sync(0xffffffffu, tOutOff, l) + pos;
+        if (outIdx >= P.cap) continue;
+        const int gpitch = __shfl_sync(0xffffffffu, tPitch, l);
+        const unsigned int imgOff = __shfl_sync(0xffffffffu, tImgOff, l);
+        const uint32_t packed = P.lvlKp[(size_t)b * P.nodeTotal + slot];
+        const int x = (int)(packed & 0xFFF) + 16, y = (int)((packed >> 12) & 0xFFF) + 16;
+        const int resp = (int)(packed >> 24);
 
-    // ---- E8: steered BRIEF on the staged blurred patch; lane <-> descriptor byte
-    const float factorPI = (float)(3.14159265358979323846 / 180.f);
-    const float ang = __fmul_rn(angle, factorPI);
-    // libm cosf/sinf on the CPU are (almost always) the correctly rounded values: take them through double
-    double sd, cd;
-    sincos_0_2pi((double)ang, &sd, &cd);
-    const float a = (float)cd, bsn = (float)sd;
-    __syncwarp();
-    const uint8_t *pc = patch + 18 * DS_PPITCH + (x - px0); // patch centre
-    int val = 0;
+        // ---- stage the blurred 37 x 37 patch (rows y-18..y+18, 16-byte chunks from (x-18) & ~15) and the un-blurred
+        //      31 x 31 one (rows y-15..y+15 from (x-15) & ~15): all 8 loads of a lane in flight together
+        const uint8_t *bl = P.blur + (size_t)b * P.pyrStride + imgOff;
+        const uint8_t *img = l ? P.pyr + (size_t)b * P.pyrStride + imgOff : P.l0 + (size_t)b * P.l0ImgStride;
+        const int ipitch = l ? gpitch : P.l0Pitch;
+        const int px0 = (x - 18) & ~15, px1 = (x - 15) & ~15;
+        __syncwarp(); // every lane is done with the previous keypoint's patches
+        {
+            uint4 v[5], u[3];
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const float4 p = sPat[k * 32 + lane];
-        const int r0 = cv_round_magic(__fadd_rn(__fmul_rn(p.x, bsn), __fmul_rn(p.y, a)));
-        const int c0 = cv_round_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, bsn)));
-        const int r1 = cv_round_magic(__fadd_rn(__fmul_rn(p.z, bsn), __fmul_rn(p.w, a)));
-        const int c1 = cv_round_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, bsn)));
-        const int t0 = pc[r0 * DS_PPITCH + c0], t1 = pc[r1 * DS_PPITCH + c1];
-        val |= (t0 < t1) << k;
-    }
-    P.desc[((size_t)b * P.cap + outIdx) * 32 + lane] = (uint8_t)val;
-
-    // ---- E9: keypoint record (== cv::KeyPoint); pt scaled to level-0 coordinates for level > 0 (:1329-1333)
-    if (lane < 7) {
-        float f;
-        const float fx = l ? __fmul_rn((float)x, g.scale) : (float)x;
-        const float fy = l ? __fmul_rn((float)y, g.scale) : (float)y;
-        switch (lane) {
-        case 0: f = fx; break;
-        case 1: f = fy; break;
-        case 2: f = g.patch; break;
-        case 3: f = angle; break;
-        case 4: f = (float)resp; break;
-        case 5: f = __int_as_float(l); break;
-        default: f = __int_as_float(-1); break;
+            for (int i = 0; i < 5; i++) {
+                const int idx = lane + 32 * i; // chunk index: row = idx / 4, chunk = idx % 4
+                const int r = idx >> 2, ch = idx & 3;
+                const int gx = px0 + (ch << 4);
+                v[i] = make_uint4(0, 0, 0, 0);
+                if (idx < DS_PROWS * 4 && gx < gpitch) v[i] = ldg_nc_v4(bl + (size_t)(y - 18 + r) * gpitch + gx);
+            }
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                const int idx = lane + 32 * i; // row = idx / 3, chunk = idx % 3
+                const int r = (idx * 171) >> 9, ch = idx - 3 * r;
+                const int gx = px1 + (ch << 4);
+                u[i] = make_uint4(0, 0, 0, 0);
+                if (idx < 31 * 3 && gx < ipitch) u[i] = ldg_nc_v4(img + (size_t)(y - 15 + r) * ipitch + gx);
+            }
+#pragma unroll
+            for (int i = 0; i < 5; i++) {
+                const int idx = lane + 32 * i;
+                if (idx < DS_PROWS * 4) *reinterpret_cast<uint4 *>(patch + (idx >> 2) * DS_PPITCH + ((idx & 3) << 4)) = v[i];
+            }
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                const int idx = lane + 32 * i;
+                if (idx < 32 * 3) *reinterpret_cast<uint4 *>(raw + idx * 16) = u[i]; // row-major 48-byte rows; row 31 = zeros
+            }
         }
-        reinterpret_cast<float *>(P.kps + (size_t)b * P.cap + outIdx)[lane] = f;
+        __syncwarp();
+
+        // ---- E6: intensity-centroid moments over the radius-15 disc of the UN-blurred level; lane <-> row v
+        int m10, m01;
+        {
+            const uint4 *rowp = reinterpret_cast<const uint4 *>(raw + lane * DS_RPITCH);
+            const uint4 q0 = rowp[0], q1 = rowp[1], q2 = rowp[2];
+            const int o = (x - 15) - px1; // first disc column inside the staged row (warp-uniform)
+            const unsigned int sb = (unsigned int)(o & 3) * 8u;
+            int s, t;
+            switch (o >> 2) {
+            case 0: disc_row_sums<0>(q0, q1, q2, sb, mk, s, t); break;
+            case 1: disc_row_sums<1>(q0, q1, q2, sb, mk, s, t); break;
+            case 2: disc_row_sums<2>(q0, q1, q2, sb, mk, s, t); break;
+            default: disc_row_sums<3>(q0, q1, q2, sb, mk, s, t); break;
+            }
+            m10 = warp_sum(t);
+            m01 = warp_sum((lane - 15) * s);
+        }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // ---- E8: steered BRIEF on the staged blurred patch; lane <-> descriptor byte
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const float ang = __fmul_rn(angle, factorPI);
+        // libm cosf/sinf on the CPU are (almost always) the correctly rounded values: take them through double
+        double sd, cd;
+        sincos_0_2pi((double)ang, &sd, &cd);
+        const float a = (float)cd, bsn = (float)sd;
+        const uint8_t *pc = patch + 18 * DS_PPITCH + (x - px0); // patch centre
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float4 p = sPat[k * 32 + lane];
+            const int r0 = cv_round_magic(__fadd_rn(__fmul_rn(p.x, bsn), __fmul_rn(p.y, a)));
+            const int c0 = cv_round_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, bsn)));
+            const int r1 = cv_round_magic(__fadd_rn(__fmul_rn(p.z, bsn), __fmul_rn(p.w, a)));
+            const int c1 = cv_round_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, bsn)));
+            const int t0 = pc[r0 * DS_PPITCH + c0], t1 = pc[r1 * DS_PPITCH + c1];
+            val |= (t0 < t1) << k;
+        }
+        P.desc[((size_t)b * P.cap + outIdx) * 32 + lane] = (uint8_t)val;
+
+        // ---- E9: keypoint record (== cv::KeyPoint); pt scaled to level-0 coordinates for level > 0 (:1329-1333)
+        const float scale = __shfl_sync(0xffffffffu, tScale, l), psize = __shfl_sync(0xffffffffu, tPatch, l);
+        if (lane < 7) {
+            float f;
+            const float fx = l ? __fmul_rn((float)x, scale) : (float)x;
+            const float fy = l ? __fmul_rn((float)y, scale) : (float)y;
+            switch (lane) {
+            case 0: f = fx; break;
+            case 1: f = fy; break;
+            case 2: f = psize; break;
+            case 3: f = angle; break;
+            case 4: f = (float)resp; break;
+            case 5: f = __int_as_float(l); break;
+            default: f = __int_as_float(-1); break;
+            }
+            reinterpret_cast<float *>(P.kps + (size_t)b * P.cap + outIdx)[lane] = f;
+        }
     }
 }
 
