@@ -30,13 +30,21 @@ __device__ __forceinline__ int reflect101(int p, int n)
     return p;
 }
 
-__device__ __forceinline__ unsigned int blur_load4(const uint8_t *row, int c, int W, bool interior)
+// REFLECT_101 row index without the loop when one reflection is enough (|overshoot| <= 6 < H - 1)
+__device__ __forceinline__ int reflect_row(int r, int H)
+{
+    if (H < 8) return reflect101(r, H);
+    r = r < 0 ? -r : r;
+    return r >= H ? 2 * (H - 1) - r : r;
+}
+
+// 4 pixels of a row: one 32-bit load for lanes inside the image, 4 byte loads at the lane's (row-independent,
+// precomputed) reflected columns for the few lanes at the left / right edge
+__device__ __forceinline__ unsigned int blur_load4(const uint8_t *row, int c, const int (&cx)[4], bool interior)
 {
     if (interior) return __ldg(reinterpret_cast<const unsigned int *>(row + c));
-    unsigned int w = 0;
-#pragma unroll
-    for (int k = 0; k < 4; k++) w |= (unsigned int)__ldg(row + reflect101(c + k, W)) << (8 * k);
-    return w;
+    return (unsigned int)__ldg(row + cx[0]) | ((unsigned int)__ldg(row + cx[1]) << 8) | ((unsigned int)__ldg(row + cx[2]) << 16) |
+           ((unsigned int)__ldg(row + cx[3]) << 24);
 }
 
 #define BL_TAPS(a, b) ((unsigned int)(a) | ((unsigned int)(b) << 8))
@@ -61,15 +69,18 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ Ex
     // lanes entirely beyond the reflected range never contribute (their neighbours' halo stays within +-3 of [0, W))
     const bool interior = c >= 0 && c + 3 < W && ((((size_t)src) | (size_t)pitch) & 3) == 0;
     const bool store = lane >= 1 && lane <= 30 && c < W;
+    int cx[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) cx[k] = (c + k < W + 3) ? reflect101(c + k, W) : 0; // columns past W + 2 feed no output
 
     unsigned int ra[7], rb[7]; // ring of 7 rows, widened: ra = (p0, p1), rb = (p2, p3) in 16-bit lanes
 #pragma unroll
     for (int k = 0; k < 6; k++) {
-        const unsigned int w = blur_load4(src + (size_t)reflect101(y0 - 3 + k, H) * pitch, c, W, interior);
+        const unsigned int w = blur_load4(src + (size_t)reflect_row(y0 - 3 + k, H) * pitch, c, cx, interior);
         ra[k] = __byte_perm(w, 0u, 0x4140);
         rb[k] = __byte_perm(w, 0u, 0x4342);
     }
-    unsigned int nxt = blur_load4(src + (size_t)reflect101(y0 + 3, H) * pitch, c, W, interior);
+    unsigned int nxt = blur_load4(src + (size_t)reflect_row(y0 + 3, H) * pitch, c, cx, interior);
     for (int base = y0; base < yEnd; base += 7) {
 #pragma unroll
         for (int k = 0; k < 7; k++) {
@@ -77,7 +88,7 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ Ex
             if (y < yEnd) { // warp-uniform
                 ra[(k + 6) % 7] = __byte_perm(nxt, 0u, 0x4140);
                 rb[(k + 6) % 7] = __byte_perm(nxt, 0u, 0x4342);
-                if (y + 1 < yEnd) nxt = blur_load4(src + (size_t)reflect101(y + 4, H) * pitch, c, W, interior);
+                if (y + 1 < yEnd) nxt = blur_load4(src + (size_t)reflect_row(y + 4, H) * pitch, c, cx, interior);
                 // vertical pass: rows y-3 .. y+3 are ring slots k .. k+6 (mod 7)
                 const unsigned int Va = 18u * (ra[k % 7] + ra[(k + 6) % 7]) + 34u * (ra[(k + 1) % 7] + ra[(k + 5) % 7]) +
                                         48u * (ra[(k + 2) % 7] + ra[(k + 4) % 7]) + 56u * ra[(k + 3) % 7];
