@@ -109,15 +109,15 @@ __device__ __forceinline__ void load_tile(uint8_t *s, int sp, const uint8_t *img
 
 // ---------------------------------------------------------------------------------------------------
 // E2  pyramid_resize: level l from level l-1, cv::resize INTER_LINEAR 8U fixed-point arithmetic
-//     (reference call site src/ORBextractor.cc:1366).  Tile = 128 x 32 outputs, 256 threads, each thread 4 adjacent
-//     pixels on 4 rows; the source footprint is staged in shared memory with 16-byte loads.
+//     (reference call site src/ORBextractor.cc:1366).  Tile = 128 x 64 outputs, 256 threads, each thread 4 adjacent
+//     pixels on 8 rows; the source footprint is staged in shared memory with 16-byte loads.
 //     ncu of the first version: issue bound (IPC 3.4) at 60 thread instructions per pixel.  Now per source row a thread
 //     reads 4 aligned words and two PRMTs with per-thread selectors turn them into the four (p[sx], p[sx+1]) pairs;
 //     each horizontal interpolation p0*a0 + p1*a1 is one DP2A (16-bit coefficients x 8-bit pixels), each vertical
 //     term (b * (H >> 4)) >> 16 one shift + one IMAD.HI against b << 16.  The result never leaves [0, 255]
 //     (a0 + a1 = b0 + b1 = 2048), so cv's saturate_cast needs no code.
 // ---------------------------------------------------------------------------------------------------
-constexpr int RZ_TW = 128, RZ_TH = 32, RZ_THREADS = 256, RZ_SMEM_PAD = 16;
+constexpr int RZ_TW = 128, RZ_TH = 64, RZ_THREADS = 256, RZ_SMEM_PAD = 16;
 
 __device__ __forceinline__ unsigned int prmt_dyn(unsigned int a, unsigned int b, unsigned int sel)
 {
