@@ -77,7 +77,7 @@ int orbb200_extract_batch(orbb200_extractor *e, const uint8_t *const *imgs, int 
 
 /* tuning of orbb200_extract_batch's copy/compute pipeline (no reference counterpart: the reference has no
  * batching): the batch is cut into chunks of `chunk_images`; chunk c's upload, its kernels (rotating over
- * `compute_streams` <= 4 CUDA streams) and chunk c-1's download overlap.  Defaults 32 and 4.
+ * `compute_streams` <= 8 CUDA streams) and chunk c-1's download overlap.  Defaults 16 and 8.
  * device_chunk_images > 0 makes orbb200_extract_batch_device cut its batch the same way (chunks joined back
  * into the handle's stream before it returns, so the call stays stream-ordered for the caller); 0 = off, the
  * default: resident batches fill the GPU kernel by kernel and chunking buys < 4 %.  With stage profiling on

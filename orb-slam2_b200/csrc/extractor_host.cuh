@@ -43,13 +43,13 @@ struct orbb200_extractor {
     // host-API pipeline (orbb200_extract_batch): copy / D2H streams, double-buffered packed staging
     // and up to PIPE_STREAMS compute streams so that the latency-bound tail of one chunk (quadtree passes) overlaps
     // the throughput-bound head of the next (all per-image workspaces are disjoint between chunks)
-    static constexpr int PIPE_STREAMS = 4;
+    static constexpr int PIPE_STREAMS = 8;
     cudaStream_t copyStream = nullptr, d2hStream = nullptr, workStream[PIPE_STREAMS] = {};
     cudaEvent_t evH2D[2] = {nullptr, nullptr}, evDone[2] = {nullptr, nullptr}, evStaged[2] = {nullptr, nullptr};
     cudaEvent_t evWork[PIPE_STREAMS] = {}, evBegin = nullptr;
     uint8_t *d_stage[2] = {nullptr, nullptr};
     size_t stageBytes = 0;
-    int pipeChunk = 32, pipeStreams = 4, devChunk = 0;
+    int pipeChunk = 16, pipeStreams = 8, devChunk = 0;
     // last call
     int lastBatch = 0, lastCap = 0;
     const uint8_t *lastL0 = nullptr;
