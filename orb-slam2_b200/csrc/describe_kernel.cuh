@@ -110,7 +110,7 @@ template <int KW> __device__ __forceinline__ void disc_row_sums(const uint4 &q0,
     }
 }
 
-__global__ void __launch_bounds__(DS_WARPS * 32) k_orient_describe(const __grid_constant__ ExtractParams P)
+__global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __grid_constant__ ExtractParams P)
 {
     __shared__ __align__(16) float4 sPat[8 * 32];                               // [bit k of the byte][lane]
     __shared__ __align__(16) uint8_t sPatch[DS_WARPS][DS_PROWS * DS_PPITCH];

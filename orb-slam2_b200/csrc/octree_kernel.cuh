@@ -51,7 +51,7 @@ __device__ __forceinline__ int key_quadrant(uint32_t k, int x0, int x1, int y0, 
 
 // workspace (ints) per (image, level): 2 node buffers (6C each) + childpos 4C + vrank C + newpos C + vis C +
 // base C + cum C = 21C; shared memory: cc 4C ints + sort keys (sortLen u64).
-__global__ void __launch_bounds__(OCT_THREADS, 4) k_octree_select(const __grid_constant__ ExtractParams P)
+__global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_constant__ ExtractParams P)
 {
     extern __shared__ __align__(16) unsigned char dsm[];
     __shared__ int scanTmp[34];
