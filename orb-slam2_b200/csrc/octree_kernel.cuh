@@ -18,7 +18,7 @@
 
 namespace orbb200 {
 
-constexpr int OCT_THREADS = 256;
+constexpr int OCT_THREADS = 256, OCT_KU = 4; // threads per block, keys per thread per trip of the per-key loops
 
 struct NodeBuf {
     int *x0, *x1, *y0, *y1, *cnt, *seq;
@@ -42,15 +42,17 @@ __device__ __forceinline__ void warp_agg_inc(int *base, int key, bool active)
     }
 }
 
-__device__ __forceinline__ int key_quadrant(uint32_t k, int x0, int x1, int y0, int y1)
+// quadrant of a key inside a node split at (xs, ys) (DivideNode, :551-609)
+__device__ __forceinline__ int key_quadrant(uint32_t k, int xs, int ys)
 {
-    const int hx = (x1 - x0 + 1) >> 1, hy = (y1 - y0 + 1) >> 1; // ceil(d / 2.f) for d >= 0 (:553-554)
     const int x = k & 0xFFF, y = (k >> 12) & 0xFFF;
-    return (x < x0 + hx ? 0 : 1) + (y < y0 + hy ? 0 : 2);
+    return (x < xs ? 0 : 1) + (y < ys ? 0 : 2);
 }
 
-// workspace (ints) per (image, level): 2 node buffers (6C each) + childpos 4C + vrank C + newpos C + vis C +
-// base C + cum C = 21C; shared memory: cc 4C ints + sort keys (sortLen u64).
+// workspace (ints) per (image, level): 2 node buffers (6C each) + vrank C + vis C + base C + cum C (21C reserved);
+// shared memory: everything the two per-key loops of a pass touch per node -- quadrant counts cc 4C, child positions
+// 4C, new positions C, split coordinates recX / recY C each (recX < 0: node not split in this pass) -- + sort keys
+// (sortLen u64).  With the node arrays in global memory a key cost a chain of three dependent L2 loads per loop.
 __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_constant__ ExtractParams P)
 {
     extern __shared__ __align__(16) unsigned char dsm[];
@@ -61,7 +63,8 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
     const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = NT >> 5;
     const int C = g.nodeCap, N = g.nfeat;
     int *cc = reinterpret_cast<int *>(dsm);                                   // [4C]
-    unsigned long long *skeys = reinterpret_cast<unsigned long long *>(dsm + (((size_t)4 * C * 4 + 15) & ~(size_t)15)); // [sortLen]
+    int *childpos = cc + 4 * C, *newpos = cc + 8 * C, *recX = cc + 9 * C, *recY = cc + 10 * C;
+    unsigned long long *skeys = reinterpret_cast<unsigned long long *>(dsm + (((size_t)11 * C * 4 + 15) & ~(size_t)15)); // [sortLen]
     const int *cellCount = P.cellCount + (size_t)b * P.totalCells + g.cellBase;
     int *cellScan = P.cellScan + (size_t)b * P.totalCells + g.cellBase;
     const uint32_t *cand = P.cand + (size_t)b * P.candStride + g.candOff;
@@ -69,8 +72,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
     int *knode = P.knode + (size_t)b * P.candStride + g.candOff;
     int *ws = P.nodeWs + (size_t)b * P.nodeWsStride + g.nodeWsOff;
     NodeBuf cur = node_buf(ws, C), nxt = node_buf(ws + 6 * C, C);
-    int *childpos = ws + 12 * C, *vrank = ws + 16 * C, *newpos = ws + 17 * C, *vis = ws + 18 * C, *basea = ws + 19 * C,
-        *cum = ws + 20 * C;
+    int *vrank = ws + 16 * C, *vis = ws + 18 * C, *basea = ws + 19 * C, *cum = ws + 20 * C;
 
     // ---- gather the cells' candidates in the reference's order (cell-row-major, row-major inside a cell)
     int n = 0;
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
                 const int f = (p < size && cur.cnt[p] > 1) ? 1 : 0;
                 int tot;
                 const int ex = block_excl_scan(f, scanTmp, &tot);
-                if (p < size) vrank[p] = f ? nvis + ex : -1;
+                if (p < size) { vrank[p] = f ? nvis + ex : -1; recX[p] = -1; }
                 if (f) vis[nvis + ex] = p;
                 nvis += tot;
             }
@@ -145,7 +147,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
                 const int f = (p < size && cur.cnt[p] > 1) ? 1 : 0;
                 int tot;
                 const int ex = block_excl_scan(f, scanTmp, &tot);
-                if (p < size) vrank[p] = -1;
+                if (p < size) { vrank[p] = -1; recX[p] = -1; }
                 if (f)
                     skeys[nvis + ex] = ((unsigned long long)cur.cnt[p] << 40) | ((unsigned long long)(cur.seq[p] & 0xFFFFF) << 20) |
                                        (unsigned long long)p;
@@ -178,20 +180,37 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
         for (int r = tid; r < nvis; r += NT) {
             const int p = vis[r];
             cc[4 * p] = 0; cc[4 * p + 1] = 0; cc[4 * p + 2] = 0; cc[4 * p + 3] = 0;
+            const int x0 = cur.x0[p], y0 = cur.y0[p];
+            recX[p] = x0 + ((cur.x1[p] - x0 + 1) >> 1); // x0 + ceil(d / 2.f) for d >= 0 (:553-554)
+            recY[p] = y0 + ((cur.y1[p] - y0 + 1) >> 1);
         }
         if (tid == 0) { sh_nexp = 0; sh_rstar = nvis - 1; }
         __syncthreads();
-        for (int i = tid; i < nPad; i += NT) {
-            int key = 0;
-            bool act = false;
-            if (i < n) {
-                const int p = knode[i];
-                if (vrank[p] >= 0) {
-                    key = 4 * p + key_quadrant(ord[i], cur.x0[p], cur.x1[p], cur.y0[p], cur.y1[p]);
-                    act = true;
-                }
+        // four keys per thread per trip: the eight loads are issued before the first dependent shared-memory read (one
+        // key at a time the loop ran at L2 latency, ~500 cycles per trip)
+        for (int i0 = tid; i0 < nPad; i0 += OCT_KU * NT) {
+            int pk[OCT_KU];
+            uint32_t ok[OCT_KU];
+#pragma unroll
+            for (int u = 0; u < OCT_KU; u++) {
+                const int i = i0 + u * NT;
+                pk[u] = i < n ? knode[i] : -1;
+                ok[u] = i < n ? ord[i] : 0u;
             }
-            warp_agg_inc(cc, key, act);
+#pragma unroll
+            for (int u = 0; u < OCT_KU; u++) {
+                if (i0 - lane + u * NT >= nPad) break; // warp-uniform: nPad and NT are multiples of 32
+                int key = 0;
+                bool act = false;
+                if (pk[u] >= 0) {
+                    const int xs = recX[pk[u]];
+                    if (xs >= 0) {
+                        key = 4 * pk[u] + key_quadrant(ok[u], xs, recY[pk[u]]);
+                        act = true;
+                    }
+                }
+                warp_agg_inc(cc, key, act);
+            }
         }
         __syncthreads();
         // (3) creation index of the children; in mode 1 also the cut (:879)
@@ -217,7 +236,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
                 if (size + cum[r] >= N) atomicMin(&sh_rstar, r);
             __syncthreads();
             nsplit = sh_rstar + 1;
-            for (int r = nsplit + tid; r < nvis; r += NT) vrank[vis[r]] = -1;
+            for (int r = nsplit + tid; r < nvis; r += NT) { vrank[vis[r]] = -1; recX[vis[r]] = -1; }
             T = nsplit > 0 ? basea[nsplit - 1] : 0;
             if (nsplit > 0) {
                 const int p = vis[nsplit - 1];
@@ -267,12 +286,22 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
         }
         __syncthreads();
         // (5) keys follow their node
-        for (int i = tid; i < n; i += NT) {
-            const int p = knode[i];
-            if (vrank[p] >= 0)
-                knode[i] = childpos[4 * p + key_quadrant(ord[i], cur.x0[p], cur.x1[p], cur.y0[p], cur.y1[p])];
-            else
-                knode[i] = newpos[p];
+        for (int i0 = tid; i0 < n; i0 += OCT_KU * NT) {
+            int pk[OCT_KU];
+            uint32_t ok[OCT_KU];
+#pragma unroll
+            for (int u = 0; u < OCT_KU; u++) {
+                const int i = i0 + u * NT;
+                pk[u] = i < n ? knode[i] : -1;
+                ok[u] = i < n ? ord[i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < OCT_KU; u++) {
+                if (pk[u] >= 0) {
+                    const int xs = recX[pk[u]];
+                    knode[i0 + u * NT] = xs >= 0 ? childpos[4 * pk[u] + key_quadrant(ok[u], xs, recY[pk[u]])] : newpos[pk[u]];
+                }
+            }
         }
         __syncthreads();
         const int newSize = T + nsurv;

@@ -85,7 +85,7 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
             nodeOff += g.nodeCap;
             g.nodeWsOff = (unsigned int)wsOff;
             wsOff += align_up((size_t)21 * g.nodeCap, 32);
-            octSmem = std::max(octSmem, align_up((size_t)16 * g.nodeCap, 16) + (size_t)8 * g.sortLen);
+            octSmem = std::max(octSmem, align_up((size_t)44 * g.nodeCap, 16) + (size_t)8 * g.sortLen);
             g.scale = e->sf[l];
             g.patch = (float)(int)(31 * e->sf[l]); // scaledPatchSize (:1023)
             g.blurTileBase = tileBase;
