@@ -230,21 +230,24 @@ __global__ void __launch_bounds__(FC_THREADS, 8) k_fast_cells(const __grid_const
     const uint32_t base0 = r1.y + (uint32_t)x + ((uint32_t)yl << 12);
     int wcnt = 0;
     const unsigned int *w = sW + g0 * 32 + lane + lpr;
+    uint32_t base = base0 + ((uint32_t)(g0 * rpw) << 12);
     for (int gi = g0; gi < g1; gi++, w += 32) {
         const unsigned int W = w[0];
-        if (!__any_sync(0xffffffffu, (W & 0xFFFFu) != 0u)) continue;
+        if (!__any_sync(0xffffffffu, (W & 0xFFFFu) != 0u)) { base += (uint32_t)rpw << 12; continue; }
         const unsigned int mx = __vmaxs2(widen_hi(w[-lpr]), widen_hi(w[lpr]));
         const unsigned int s = widen_lo(W);
         const unsigned int sk = s & ~neg_mask2(bsub2(mx, s)); // s' where it also beats the rows above and below
-        const unsigned int lo = sk & 0xFFFFu, hi = sk >> 16;
-        const unsigned int bl = __ballot_sync(0xffffffffu, lo != 0u), bh = __ballot_sync(0xffffffffu, hi != 0u);
+        // the two pixels of a pair are neighbours, so at most one of them is a strict local maximum: one ballot,
+        // one entry per lane
+        const unsigned int bs = __ballot_sync(0xffffffffu, sk != 0u);
         if (sk != 0u) {
-            int pos = wcnt + __popc(bl & lt) + __popc(bh & lt);
-            const uint32_t base = base0 + ((uint32_t)(gi * rpw) << 12);
-            if (lo != 0u && pos < FC_LISTCAP) list[pos++] = base | (lo << 24);
-            if (hi != 0u && pos < FC_LISTCAP) list[pos] = (base + 1u) | (hi << 24);
+            const int pos = wcnt + __popc(bs & lt);
+            const unsigned int hi = sk >> 16; // 0 when the survivor is the low pixel
+            if (pos < FC_LISTCAP)
+                list[pos] = (base + (hi ? 1u : 0u)) | ((sk | hi) << 24); // score << 24: bits above 31 fall off
         }
-        wcnt += __popc(bl) + __popc(bh);
+        wcnt += __popc(bs);
+        base += (uint32_t)rpw << 12;
     }
     wcnt = min(wcnt, FC_LISTCAP);
     __syncwarp();
