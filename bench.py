@@ -10,7 +10,7 @@ One step = one pass of the hot path over one batch of P synthetic KITTI-shape st
 1241x376, 2000 features, 8 levels, FAST 20/7): pyramid -> FAST cells -> quadtree -> blur -> orientation +
 descriptors for all 2P images, then Frame::ComputeStereoMatches for the P pairs.  Frames are sharded over the ranks
 (weak scaling, no data-path collective).  `value` = images/s with inputs resident in HBM; `e2e` = images/s through
-the host-buffer C-ABI (orbb200_extract_batch + orbb200_stereo_match_batch) with pinned host inputs/outputs and
+the host-buffer C-ABI (orbb200_extract_stereo_batch) with pinned host inputs/outputs and
 all H2D/D2H copies inside the timed region.  The `match` object is BASELINE config 5 (2 048 queries x 1 048 576
 database rows, database row-sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge kernel).
 
@@ -306,8 +306,9 @@ def run_b200(args, rank, world, local_rank):
     L = orbb200.lib()
 
     def step_host():
-        orbb200.check(L.orbb200_extract_batch(ex.h, ptrs, B, w, h, w, kps_h.data_ptr(), desc_h.data_ptr(), cap, n_h.data_ptr()))
-        orbb200.check(L.orbb200_stereo_match_batch(ex.h, P, K["bf"], bconst, uR_h.data_ptr(), dep_h.data_ptr(), nv_h.data_ptr()))
+        # the stereo Frame constructor's feature work as one call: extraction of L and R + ComputeStereoMatches
+        orbb200.check(L.orbb200_extract_stereo_batch(ex.h, ptrs, P, w, h, w, kps_h.data_ptr(), desc_h.data_ptr(), cap, n_h.data_ptr(),
+                                                     K["bf"], bconst, uR_h.data_ptr(), dep_h.data_ptr(), nv_h.data_ptr()))
 
     for _ in range(2):
         step_host()
@@ -339,7 +340,7 @@ def run_b200(args, rank, world, local_rank):
                    "inputs smaller than L2: raise --pairs", "mean_keypoints_per_image": mean_kp,
                    "mean_stereo_matches_per_pair": float(nv_host.mean()), "sharding": "frames per GPU, no collective"},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "api": "orbb200_extract_batch + orbb200_stereo_match_batch (pinned host buffers)"},
+                "steps": e2e_steps, "api": "orbb200_extract_stereo_batch (pinned host buffers; extraction L+R + ComputeStereoMatches in one pipelined call)"},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": roofline,
         "clocks": sampler.summary(),

@@ -181,6 +181,16 @@ int orbb200_stereo_match_batch(orbb200_extractor *e, int npairs, float bf, float
 int orbb200_stereo_match_batch_device(orbb200_extractor *e, int npairs, float bf, float b, float *uRight_d,
                                       float *depth_d, int *n_valid_d);
 
+/* replaces the stereo Frame constructor's feature work as ONE call (src/Frame.cc:60-117: ExtractORB left / right on
+ * two threads, :82-85, then ComputeStereoMatches, :94) for `npairs` stereo pairs: imgs[2p] is the left and
+ * imgs[2p+1] the right image of pair p (2*npairs host images of one shape).  Extraction outputs as
+ * orbb200_extract_batch (kps, desc, n_out for 2*npairs images); uRight / depth are host [npairs][cap], n_valid
+ * [npairs].  Same results as orbb200_extract_batch followed by orbb200_stereo_match_batch; here each chunk's pairs
+ * are matched on the chunk's stream right behind its extraction, inside the copy/compute pipeline. */
+int orbb200_extract_stereo_batch(orbb200_extractor *e, const uint8_t *const *imgs, int npairs, int width, int height,
+                                 int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out, float bf, float b,
+                                 float *uRight, float *depth, int *n_valid);
+
 /* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
  * roofline; runs a dependent-free popc microkernel for a few milliseconds. */
 int orbb200_popc_peak(int device, double *popc32_per_s);

@@ -39,7 +39,7 @@ struct orbb200_extractor {
     float *d_stU = nullptr, *d_stD = nullptr;
     int *d_stSad = nullptr, *d_stN = nullptr, *d_stRows = nullptr;
     size_t stElems = 0, stRowElems = 0;
-    int stPairs = 0;
+    int stPairs = 0, stOutCap = 0;
     // host-API pipeline (orbb200_extract_batch): copy / D2H streams, double-buffered packed staging
     // and up to PIPE_STREAMS compute streams so that the latency-bound tail of one chunk (quadtree passes) overlaps
     // the throughput-bound head of the next (all per-image workspaces are disjoint between chunks)
@@ -72,4 +72,10 @@ int extractor_ensure_outputs(orbb200_extractor *e, int batch, int cap);
 int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes);
 int extractor_run(orbb200_extractor *e, const uint8_t *l0, size_t l0ImgStride, int l0Pitch, int l0Valid, int batch,
                   orbb200_keypoint *kps_d, uint8_t *desc_d, int cap, int *nOut_d);
+// batched stereo matcher pieces shared by orbb200_match.cu (owner) and the fused extract + stereo pipeline
+int stereo_ensure_scratch(orbb200_extractor *e, int npairs, int cap);
+int stereo_ensure_outputs(orbb200_extractor *e, int npairs, int cap);
+int stereo_batch_range(orbb200_extractor *e, const orbb200_keypoint *kps, const uint8_t *desc, const int *nOut, const uint8_t *l0,
+                       int l0Pitch, size_t l0ImgStride, int cap, int pair0, int npairs, int totalPairs, float bf, float b,
+                       float *uRight_d, float *depth_d, int *n_valid_d, cudaStream_t st);
 } // namespace orbb200

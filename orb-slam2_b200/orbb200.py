@@ -24,7 +24,7 @@ EXPORTS = [
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
     "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_window_search", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
-    "orbb200_stereo_match_batch_device", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
+    "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
 ]
 
 _lib = None
@@ -76,6 +76,7 @@ def lib():
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
     L.orbb200_stereo_match_batch.argtypes = [vp, ip, fp, fp, vp, vp, vp]
     L.orbb200_stereo_match_batch_device.argtypes = [vp, ip, fp, fp, vp, vp, vp]
+    L.orbb200_extract_stereo_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, fp, fp, vp, vp, vp]
     L.orbb200_popc_peak.argtypes = [ip, C.POINTER(C.c_double)]
     _lib = L
     return L
@@ -169,6 +170,21 @@ class ORBextractor:
             n_out = np.zeros(B, np.int32)
         check(self.L.orbb200_extract_batch(self.h, ptrs, B, w, h, stride, _p(kps), _p(desc), self.cap, _p(n_out)))
         return kps, desc, n_out
+
+    def extract_stereo_batch(self, images, bf, b):
+        """images: [2P,H,W] uint8 (host), pair p = (2p, 2p+1).  Extraction + ComputeStereoMatches in one pipelined call.
+        Returns (kps, desc, n, uRight[P,cap], depth[P,cap], n_valid[P])."""
+        B, h, w = images.shape
+        ptrs = (C.c_void_p * B)(*[images.ctypes.data + i * images.strides[0] for i in range(B)])
+        kps = np.zeros((B, self.cap), KP_DTYPE)
+        desc = np.zeros((B, self.cap, 32), np.uint8)
+        n_out = np.zeros(B, np.int32)
+        uR = np.zeros((B // 2, self.cap), np.float32)
+        depth = np.zeros((B // 2, self.cap), np.float32)
+        nv = np.zeros(B // 2, np.int32)
+        check(self.L.orbb200_extract_stereo_batch(self.h, ptrs, B // 2, w, h, images.strides[1], _p(kps), _p(desc), self.cap, _p(n_out),
+                                                  bf, b, _p(uR), _p(depth), _p(nv)))
+        return kps, desc, n_out, uR, depth, nv
 
     def extract_batch_device(self, imgs_ptr, batch, width, height, stride, image_stride, kps_ptr, desc_ptr, cap, n_ptr):
         check(self.L.orbb200_extract_batch_device(self.h, imgs_ptr, batch, width, height, stride, image_stride,

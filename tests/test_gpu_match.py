@@ -163,3 +163,28 @@ def test_window_search_equals_oracle_grid_and_area(configs):
         assert np.array_equal(dist[offs[q]:offs[q + 1]], d), q
         total += len(ref)
     assert offs[0] == 0 and offs[-1] == total and total > 5000 and offs[1] == 0
+
+
+def test_fused_extract_stereo_equals_two_calls(configs):
+    """orbb200_extract_stereo_batch (the stereo Frame constructor as one pipelined call) == orbb200_extract_batch followed by
+    orbb200_stereo_match_batch, for several chunkings of the pipeline (odd chunk sizes are rounded to whole pairs)."""
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    P = 5
+    imgs = np.empty((2 * P, h, w), np.uint8)
+    for p in range(P):
+        imgs[2 * p], imgs[2 * p + 1] = synth.stereo_pair(w, h, 7000 + p)
+    bf, b = 386.1448, 386.1448 / 718.856
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kps0, desc0, n0 = ex.extract_batch(imgs)
+    uR0, dep0, nv0 = ex.stereo_match_batch(P, bf, b)
+    assert nv0.min() > 100
+    for chunk, ns in [(16, 8), (2, 3), (5, 2), (4, 8)]:
+        ex2 = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+        ex2.set_pipeline(chunk, ns, 0)
+        kps, desc, n, uR, dep, nv = ex2.extract_stereo_batch(imgs, bf, b)
+        assert np.array_equal(n, n0) and np.array_equal(nv, nv0), (chunk, ns)
+        for i in range(2 * P):
+            assert np.array_equal(kps[i, :n[i]].view(np.uint8), kps0[i, :n[i]].view(np.uint8)) and np.array_equal(desc[i, :n[i]], desc0[i, :n[i]])
+        for p in range(P):
+            nl_ = n[2 * p]
+            assert np.array_equal(uR[p, :nl_], uR0[p, :nl_]) and np.array_equal(dep[p, :nl_], dep0[p, :nl_]), (chunk, ns, p)
