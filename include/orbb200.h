@@ -191,6 +191,52 @@ int orbb200_extract_stereo_batch(orbb200_extractor *e, const uint8_t *const *img
                                  int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out, float bf, float b,
                                  float *uRight, float *depth, int *n_valid);
 
+/* ---- DBoW2 vocabulary transform (Frame::ComputeBoW, src/Frame.cc:459-466; KeyFrame::ComputeBoW, src/KeyFrame.cc:59-69) ----
+ * ORBVocabulary = DBoW2::TemplatedVocabulary<cv::Mat, FORB> (include/ORBVocabulary.h:31-32); file:line below are under
+ * Thirdparty/DBoW2/DBoW2/.  scoring / weighting use the reference's enum values (BowVector.h:36-53):
+ * weighting 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY; scoring 0 L1_NORM ... 5 DOT_PRODUCT. */
+typedef struct orbb200_vocabulary orbb200_vocabulary; /* opaque; the tree resident in HBM + one CUDA stream */
+
+/* replaces TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1358-1443): first line "k L scoring weighting",
+ * then one line per node, ids 1, 2, ... in line order: "parent isLeaf b0 .. b31 weight".  Same header checks as the
+ * reference (:1385-1389 -> ORBB200_ERR_ARG).  Blank lines are skipped: the reference turns the empty string after the
+ * final newline into a phantom child of the root with an uninitialised descriptor (while(!f.eof()) + getline). */
+int orbb200_vocabulary_load_text(orbb200_vocabulary **out, const char *path, int device);
+/* the same tree from arrays (what the loader builds): node 0 is the root; for n in 1..nnodes-1 parent[n] < n, children
+ * are ordered by id (m_nodes[pid].children.push_back(nid), :1411), is_leaf[n] != 0 marks a word and words are numbered
+ * in id order (:1430-1437); desc is [nnodes][32], weight [nnodes] (rows 0 are ignored).  A word with children or an
+ * inner node without children is rejected (the reference would walk off an empty child list). */
+int orbb200_vocabulary_create(orbb200_vocabulary **out, int k, int L, int scoring, int weighting, int nnodes,
+                              const int *parent, const uint8_t *is_leaf, const uint8_t *desc, const double *weight,
+                              int device);
+void orbb200_vocabulary_destroy(orbb200_vocabulary *v);
+/* getBranchingFactor / getDepthLevels / m_scoring / m_weighting / m_nodes.size() / size() (:83, :146-152) */
+int orbb200_vocabulary_info(const orbb200_vocabulary *v, int *k, int *L, int *scoring, int *weighting, int *nnodes,
+                            int *nwords);
+
+/* replaces transform(feature, word_id, weight, nid, levelsup) (:1218-1259) for n descriptors (host [n][32]): the walk
+ * from the root to a word, nearest child first-on-ties at every node.  node_id[i] is the node of feature i's path at
+ * level L - levelsup (0 when that level is <= 0); where the word lies above that level the reference leaves *nid
+ * unwritten, here it is the word's own node id. */
+int orbb200_vocabulary_transform(orbb200_vocabulary *v, const uint8_t *desc, int n, int levelsup, int *word_id,
+                                 double *weight, int *node_id);
+/* same with device pointers (desc_d 16-byte aligned, e.g. the descriptor block orbb200_extract_batch_device wrote),
+ * asynchronous on `stream` (a cudaStream_t; NULL = the vocabulary's own stream). */
+int orbb200_vocabulary_transform_device(orbb200_vocabulary *v, const uint8_t *desc_d, int n, int levelsup,
+                                        int *word_id_d, double *weight_d, int *node_id_d, void *stream);
+
+/* replaces transform(features, BowVector, FeatureVector, levelsup) (:1127-1190) -- what Frame::ComputeBoW calls with
+ * levelsup = 4 -- for nimg images in one call: desc holds the images' descriptor rows back to back, counts[i] rows for
+ * image i.  The tree walks of all images run as one launch; the std::map contents come back flattened in key order:
+ *   BowVector of image i    = (bow_id[j], bow_val[j])                       for j in [bow_off[i], bow_off[i+1])
+ *   FeatureVector of image i = fv_node[j] -> fv_feat[fv_feat_off[j] .. fv_feat_off[j+1])  for j in [fv_off[i], fv_off[i+1])
+ * with feature indices local to the image and ascending (addFeature's push_back order, FeatureVector.cpp:31-45).
+ * Values follow BowVector.cpp:34-84 in double, term by term in the reference's order (addWeight in feature order,
+ * normalize in word order).  Every output array needs room for sum(counts) entries (+1 for the *_off arrays). */
+int orbb200_compute_bow_batch(orbb200_vocabulary *v, const uint8_t *desc, const int *counts, int nimg, int levelsup,
+                              int *bow_off, int *bow_id, double *bow_val, int *fv_off, int *fv_node, int *fv_feat_off,
+                              int *fv_feat);
+
 /* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
  * roofline; runs a dependent-free popc microkernel for a few milliseconds. */
 int orbb200_popc_peak(int device, double *popc32_per_s);

@@ -103,6 +103,12 @@ public:
         for (int r = 0; r < rows; r++) std::memcpy(m.ptr(r), ptr(r), (size_t)cols * esz(type_));
         return m;
     }
+    static Mat zeros(int r, int c, int type)
+    {
+        Mat m(r, c, type);
+        std::memset(m.data, 0, m.step * (size_t)(r > 0 ? r : 0));
+        return m;
+    }
     const Mat &getMat() const { return *this; } /* so `_image.getMat()` style code keeps compiling */
 
 private:

@@ -25,6 +25,8 @@ EXPORTS = [
     "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_window_search", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
     "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
+    "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
+    "orbb200_vocabulary_transform", "orbb200_vocabulary_transform_device", "orbb200_compute_bow_batch",
 ]
 
 _lib = None
@@ -78,6 +80,14 @@ def lib():
     L.orbb200_stereo_match_batch_device.argtypes = [vp, ip, fp, fp, vp, vp, vp]
     L.orbb200_extract_stereo_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, fp, fp, vp, vp, vp]
     L.orbb200_popc_peak.argtypes = [ip, C.POINTER(C.c_double)]
+    L.orbb200_vocabulary_load_text.argtypes = [C.POINTER(vp), C.c_char_p, ip]
+    L.orbb200_vocabulary_create.argtypes = [C.POINTER(vp), ip, ip, ip, ip, ip, vp, vp, vp, vp, ip]
+    L.orbb200_vocabulary_destroy.argtypes = [vp]
+    L.orbb200_vocabulary_destroy.restype = None
+    L.orbb200_vocabulary_info.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    L.orbb200_vocabulary_transform.argtypes = [vp, vp, ip, ip, vp, vp, vp]
+    L.orbb200_vocabulary_transform_device.argtypes = [vp, vp, ip, ip, vp, vp, vp, vp]
+    L.orbb200_compute_bow_batch.argtypes = [vp, vp, vp, ip, ip, vp, vp, vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -330,6 +340,101 @@ class ORBmatcher:
         b = top2["best_dist"].astype(np.float32)
         s = top2["second_dist"].astype(np.float32)
         return (top2["best_dist"] <= th) & (b < self.mfNNratio * s)
+
+
+class ORBVocabulary:
+    """ORB_SLAM2::ORBVocabulary (include/ORBVocabulary.h:31-32 = DBoW2::TemplatedVocabulary<cv::Mat, FORB>): the tree
+    lives in HBM, transform() walks a batch of descriptors on the GPU."""
+
+    def __init__(self, device=-1):
+        self.h = C.c_void_p()
+        self.device = device
+
+    def _drop(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            lib().orbb200_vocabulary_destroy(self.h)
+            self.h = C.c_void_p()
+
+    close = _drop
+
+    def __del__(self):
+        try:
+            self._drop()
+        except Exception:
+            pass
+
+    def loadFromTextFile(self, path):
+        """TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1358-1443); False on a bad file like the reference."""
+        self._drop()
+        rc = lib().orbb200_vocabulary_load_text(C.byref(self.h), path.encode(), self.device)
+        if rc == -2:
+            check(rc)
+        return rc == 0
+
+    @classmethod
+    def from_arrays(cls, k, L, scoring, weighting, parent, is_leaf, desc, weight, device=-1):
+        v = cls(device)
+        parent = np.ascontiguousarray(parent, dtype=np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, dtype=np.uint8)
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        weight = np.ascontiguousarray(weight, dtype=np.float64)
+        check(lib().orbb200_vocabulary_create(C.byref(v.h), k, L, scoring, weighting, len(parent), _p(parent), _p(is_leaf), _p(desc),
+                                              _p(weight), device))
+        return v
+
+    def info(self):
+        a = np.zeros(6, np.int32)
+        check(lib().orbb200_vocabulary_info(self.h, *[C.c_void_p(a.ctypes.data + 4 * i) for i in range(6)]))
+        return dict(zip(("k", "L", "scoring", "weighting", "nodes", "words"), [int(x) for x in a]))
+
+    def size(self):
+        return self.info()["words"]
+
+    def empty(self):
+        return self.size() == 0
+
+    def transform_features(self, desc, levelsup=0):
+        """per-feature transform(feature, word_id, weight, nid, levelsup) (:1218-1259) for every row of desc."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        n = len(desc)
+        word, weight, nid = np.zeros(n, np.int32), np.zeros(n, np.float64), np.zeros(n, np.int32)
+        check(lib().orbb200_vocabulary_transform(self.h, _p(desc), n, levelsup, _p(word), _p(weight), _p(nid)))
+        return word, weight, nid
+
+    def transform_features_device(self, desc_ptr, n, levelsup, word_ptr, weight_ptr, nid_ptr, stream=None):
+        check(lib().orbb200_vocabulary_transform_device(self.h, C.c_void_p(desc_ptr), n, levelsup, C.c_void_p(word_ptr),
+                                                        C.c_void_p(weight_ptr), C.c_void_p(nid_ptr), C.c_void_p(stream or 0)))
+
+    def compute_bow_batch_raw(self, desc, counts, levelsup=4):
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        assert int(counts.sum()) == len(desc)
+        n, m = len(desc), len(counts)
+        out = dict(bow_off=np.zeros(m + 1, np.int32), bow_id=np.zeros(n + 1, np.int32), bow_val=np.zeros(n + 1, np.float64),
+                   fv_off=np.zeros(m + 1, np.int32), fv_node=np.zeros(n + 1, np.int32), fv_feat_off=np.zeros(n + 2, np.int32),
+                   fv_feat=np.zeros(n + 1, np.int32))
+        check(lib().orbb200_compute_bow_batch(self.h, _p(desc), _p(counts), m, levelsup, _p(out["bow_off"]), _p(out["bow_id"]),
+                                              _p(out["bow_val"]), _p(out["fv_off"]), _p(out["fv_node"]), _p(out["fv_feat_off"]),
+                                              _p(out["fv_feat"])))
+        return out
+
+    def compute_bow_batch(self, desc, counts, levelsup=4):
+        """Frame::ComputeBoW (src/Frame.cc:459-466) for a batch: [(BowVector dict, FeatureVector dict)] per image."""
+        r = self.compute_bow_batch_raw(desc, counts, levelsup)
+        res = []
+        for i in range(len(counts)):
+            b0, b1 = r["bow_off"][i], r["bow_off"][i + 1]
+            bow = {int(k): float(v) for k, v in zip(r["bow_id"][b0:b1], r["bow_val"][b0:b1])}
+            fv = {}
+            for j in range(r["fv_off"][i], r["fv_off"][i + 1]):
+                fv[int(r["fv_node"][j])] = [int(x) for x in r["fv_feat"][r["fv_feat_off"][j]:r["fv_feat_off"][j + 1]]]
+            res.append((bow, fv))
+        return res
+
+    def transform(self, desc, levelsup=4):
+        """transform(features, BowVector, FeatureVector, levelsup) (:1127-1190) for one image."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        return self.compute_bow_batch(desc, [len(desc)], levelsup)[0]
 
 
 def stereo_match(left, right, bf, b):
