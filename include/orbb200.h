@@ -237,6 +237,17 @@ int orbb200_compute_bow_batch(orbb200_vocabulary *v, const uint8_t *desc, const 
                               int *bow_off, int *bow_id, double *bow_val, int *fv_off, int *fv_node, int *fv_feat_off,
                               int *fv_feat);
 
+/* the same fold with everything resident in HBM, asynchronous on `stream` (a cudaStream_t; NULL = the vocabulary's
+ * own): desc_d is [nimg][cap][32] with n_d[i] valid rows per image -- exactly what orbb200_extract_batch_device wrote --
+ * so extraction -> ComputeStereoMatches -> ComputeBoW chain on one stream without a host round trip.  Outputs are
+ * [nimg][cap] blocks: image i's BowVector is (bow_id_d, bow_val_d)[i*cap .. + n_bow_d[i]) in word order; its
+ * FeatureVector is fv_key_d[i*cap .. + n_kept_d[i]) = (node id << 32 | feature index) ascending, i.e. node groups in
+ * map order with ascending feature lists.  cap <= 8192.  The handle's per-feature scratch is shared: keep one call in
+ * flight per vocabulary. */
+int orbb200_compute_bow_batch_device(orbb200_vocabulary *v, const uint8_t *desc_d, const int *n_d, int nimg, int cap,
+                                     int levelsup, int *bow_id_d, double *bow_val_d, int *n_bow_d,
+                                     unsigned long long *fv_key_d, int *n_kept_d, void *stream);
+
 /* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
  * roofline; runs a dependent-free popc microkernel for a few milliseconds. */
 int orbb200_popc_peak(int device, double *popc32_per_s);

@@ -39,6 +39,8 @@ struct orbb200_vocabulary {
 
 namespace orbb200 {
 
+constexpr int VOCAB_WALK_MIN_FEATURES = 16384; // measured crossover on B200 (tools/bow_probe.py): 2000 features 15 vs 21 us, 640k 0.245 vs 0.142 ms
+
 static int vocab_ensure_staging(orbb200_vocabulary *v, int n)
 {
     if (n <= v->cap) return ORBB200_OK;
@@ -95,18 +97,23 @@ static int vocab_ensure_fold(orbb200_vocabulary *v, int total, int nimg)
 }
 
 static int vocab_launch(orbb200_vocabulary *v, const uint8_t *desc_d, int n, int levelsup, int *word_d, double *w_d, int *nid_d,
-                        cudaStream_t st)
+                        cudaStream_t st, const int *counts_d = nullptr, int stride = 0)
 {
     if (n == 0) return ORBB200_OK;
     const int nidLevel = v->L - levelsup; // const int nid_level = m_L - levelsup; (:1226)
-    if (v->maxChildren <= 16) {
-        const int per = VT_THREADS / 16;
-        k_vocab_transform<16><<<div_up(n, per), VT_THREADS, 0, st>>>(v->d_desc, v->d_info, v->d_orig, v->d_weight, (const uint4 *)desc_d, n,
-                                                                     nidLevel, word_d, w_d, nid_d);
+    // Same walk, two mappings (identical results): a batch keeps every lane busy with its own feature (k_vocab_walk,
+    // L1-request bound); a single frame is latency bound, so a lane group per feature does each level in one load round.
+    if (n >= VOCAB_WALK_MIN_FEATURES) {
+        k_vocab_walk<<<div_up(n, VW_THREADS), VW_THREADS, 0, st>>>(v->d_desc, v->d_info, v->d_orig, v->d_weight, (const uint4 *)desc_d, n,
+                                                                   nidLevel, word_d, w_d, nid_d, counts_d, stride);
+    } else if (v->maxChildren <= 16) {
+        k_vocab_transform<16><<<div_up(n, VT_THREADS / 16), VT_THREADS, 0, st>>>(v->d_desc, v->d_info, v->d_orig, v->d_weight,
+                                                                                 (const uint4 *)desc_d, n, nidLevel, word_d, w_d, nid_d,
+                                                                                 counts_d, stride);
     } else {
-        const int per = VT_THREADS / 32;
-        k_vocab_transform<32><<<div_up(n, per), VT_THREADS, 0, st>>>(v->d_desc, v->d_info, v->d_orig, v->d_weight, (const uint4 *)desc_d, n,
-                                                                     nidLevel, word_d, w_d, nid_d);
+        k_vocab_transform<32><<<div_up(n, VT_THREADS / 32), VT_THREADS, 0, st>>>(v->d_desc, v->d_info, v->d_orig, v->d_weight,
+                                                                                 (const uint4 *)desc_d, n, nidLevel, word_d, w_d, nid_d,
+                                                                                 counts_d, stride);
     }
     ORB_CUDA_OK(cudaGetLastError());
     return ORBB200_OK;
@@ -364,6 +371,7 @@ int orbb200_compute_bow_batch(orbb200_vocabulary *v, const uint8_t *desc, const 
     if (rc) return rc;
     BowFoldParams P;
     P.word = v->d_word; P.nid = v->d_nid; P.weight = v->d_w; P.imgOff = v->d_imgOff;
+    P.counts = nullptr; P.stride = 0;
     P.tf = (v->weighting == 0 || v->weighting == 1) ? 1 : 0; // TF_IDF || TF (:1144)
     int norm = 1;
     P.must = must_normalize(v->scoring, &norm) ? 1 : 0;
@@ -401,6 +409,47 @@ int orbb200_compute_bow_batch(orbb200_vocabulary *v, const uint8_t *desc, const 
         fv_feat_off[nf] = nff;
         fv_off[im + 1] = nf;
     }
+    return ORBB200_OK;
+}
+
+int orbb200_compute_bow_batch_device(orbb200_vocabulary *v, const uint8_t *desc_d, const int *n_d, int nimg, int cap, int levelsup,
+                                     int *bow_id_d, double *bow_val_d, int *n_bow_d, unsigned long long *fv_key_d, int *n_kept_d,
+                                     void *stream)
+{
+    ORB_ARG_OK(v && nimg >= 0 && cap > 0, "null vocabulary / bad sizes");
+    ORB_ARG_OK(nimg == 0 || (desc_d && n_d && bow_id_d && bow_val_d && n_bow_d && fv_key_d && n_kept_d), "null argument");
+    ORB_ARG_OK(((uintptr_t)desc_d & 15) == 0, "desc_d must be 16-byte aligned");
+    ORB_ARG_OK((long long)nimg * cap < (1ll << 31), "too many descriptor rows for one call");
+    if (v->nwords == 0) { set_error("orbb200_compute_bow_batch_device: empty vocabulary"); return ORBB200_ERR_STATE; }
+    if (nimg == 0) return ORBB200_OK;
+    int npad = 2;
+    while (npad < cap) npad <<= 1;
+    const size_t smem = (size_t)npad * 16;
+    if (smem > 200 * 1024) {
+        set_error("orbb200_compute_bow_batch_device: cap %d exceeds the fold kernel's shared memory (max 8192)", cap);
+        return ORBB200_ERR_CAPACITY;
+    }
+    ORB_CUDA_OK(cudaSetDevice(v->device));
+    const int n = nimg * cap;
+    int rc = vocab_ensure_staging(v, n); // per-feature (word, weight, node) scratch
+    if (rc) return rc;
+    if ((int)smem > v->foldSmemOptIn) {
+        if (smem > 48 * 1024) ORB_CUDA_OK(cudaFuncSetAttribute(k_bow_fold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        v->foldSmemOptIn = (int)smem;
+    }
+    cudaStream_t st = stream ? (cudaStream_t)stream : v->stream;
+    rc = vocab_launch(v, desc_d, n, levelsup, v->d_word, v->d_w, v->d_nid, st, n_d, cap);
+    if (rc) return rc;
+    BowFoldParams P;
+    P.word = v->d_word; P.nid = v->d_nid; P.weight = v->d_w; P.imgOff = nullptr;
+    P.counts = n_d; P.stride = cap;
+    P.tf = (v->weighting == 0 || v->weighting == 1) ? 1 : 0;
+    int norm = 1;
+    P.must = must_normalize(v->scoring, &norm) ? 1 : 0;
+    P.norm = norm;
+    P.bowId = bow_id_d; P.bowVal = bow_val_d; P.fvKey = fv_key_d; P.nBow = n_bow_d; P.nKept = n_kept_d;
+    k_bow_fold<<<nimg, BF_THREADS, smem, st>>>(P, npad);
+    ORB_CUDA_OK(cudaGetLastError());
     return ORBB200_OK;
 }
 

@@ -18,16 +18,29 @@ namespace orbb200 {
 
 constexpr int VT_THREADS = 256;
 
+// one 32-byte node descriptor in ONE request (LDG.E.256, sm_100): half the L1 wavefronts of two 16-byte loads
+__device__ __forceinline__ void ldg_desc256(const uint4 *p, uint4 &a, uint4 &b)
+{
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+        : "l"(p));
+}
+
 template <int G>
 __global__ void __launch_bounds__(VT_THREADS)
 k_vocab_transform(const uint4 *__restrict__ nodeDesc, const int2 *__restrict__ nodeInfo, const int *__restrict__ nodeOrig,
                   const double *__restrict__ nodeWeight, const uint4 *__restrict__ feats, int n, int nidLevel,
-                  int *__restrict__ wordOut, double *__restrict__ weightOut, int *__restrict__ nidOut)
+                  int *__restrict__ wordOut, double *__restrict__ weightOut, int *__restrict__ nidOut,
+                  const int *__restrict__ counts, int stride)
 {
     const unsigned lane = threadIdx.x & 31u, gl = lane & (G - 1), gbase = lane & ~(unsigned)(G - 1);
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << gbase);
     const int f = blockIdx.x * (VT_THREADS / G) + (int)(threadIdx.x / G);
     if (f >= n) return; // group-uniform
+    if (counts) { // strided batch ([image][stride] rows, counts[image] of them valid): skip the unused rows
+        const int img = f / stride;
+        if (f - img * stride >= __ldg(counts + img)) return;
+    }
 
     const uint4 f0 = __ldg(feats + 2 * (size_t)f), f1 = __ldg(feats + 2 * (size_t)f + 1);
     const int2 root = __ldg(nodeInfo);
@@ -37,9 +50,11 @@ k_vocab_transform(const uint4 *__restrict__ nodeDesc, const int2 *__restrict__ n
         ++level;
         unsigned best = 0xffffffffu;
         int2 mine = make_int2(0, 0);
+#pragma unroll 3
         for (int c = (int)gl; c < cnt; c += G) {
             const int id = base + c;
-            const uint4 a = __ldg(nodeDesc + 2 * (size_t)id), b = __ldg(nodeDesc + 2 * (size_t)id + 1);
+            uint4 a, b;
+            ldg_desc256(nodeDesc + 2 * (size_t)id, a, b);
             const int2 inf = __ldg(nodeInfo + id);
             const int d = __popc(a.x ^ f0.x) + __popc(a.y ^ f0.y) + __popc(a.z ^ f0.z) + __popc(a.w ^ f0.w) +
                           __popc(b.x ^ f1.x) + __popc(b.y ^ f1.y) + __popc(b.z ^ f1.z) + __popc(b.w ^ f1.w);
@@ -60,6 +75,49 @@ k_vocab_transform(const uint4 *__restrict__ nodeDesc, const int2 *__restrict__ n
         // a word above the nid level: *nid is never written by the reference (indeterminate); filed under the word's own node
         nidOut[f] = __ldg(nodeOrig + (nidNode < 0 ? cur : nidNode));
     }
+}
+
+// Thread-per-feature variant: one thread scans all children of a node itself (the reference's loop, strict `<` keeps the
+// first minimum), so a level costs no shuffles / redux and every issued POPC is useful; the children's 32-byte records
+// are whole sectors, so per-thread loads waste no bandwidth.
+constexpr int VW_THREADS = 128;
+
+__global__ void __launch_bounds__(VW_THREADS)
+k_vocab_walk(const uint4 *__restrict__ nodeDesc, const int2 *__restrict__ nodeInfo, const int *__restrict__ nodeOrig,
+             const double *__restrict__ nodeWeight, const uint4 *__restrict__ feats, int n, int nidLevel,
+             int *__restrict__ wordOut, double *__restrict__ weightOut, int *__restrict__ nidOut,
+             const int *__restrict__ counts, int stride)
+{
+    const int f = blockIdx.x * VW_THREADS + (int)threadIdx.x;
+    if (f >= n) return;
+    if (counts) {
+        const int img = f / stride;
+        if (f - img * stride >= __ldg(counts + img)) return;
+    }
+    const uint4 f0 = __ldg(feats + 2 * (size_t)f), f1 = __ldg(feats + 2 * (size_t)f + 1);
+    const int2 root = __ldg(nodeInfo);
+    int base = root.x, cnt = root.y, cur = 0, level = 0;
+    int nidNode = nidLevel <= 0 ? 0 : -1;
+    while (cnt > 0) {
+        ++level;
+        int best = 1 << 30, bi = 0;
+#pragma unroll 5
+        for (int c = 0; c < cnt; c++) {
+            uint4 a, b;
+            ldg_desc256(nodeDesc + 2 * (size_t)(base + c), a, b);
+            const int d = __popc(a.x ^ f0.x) + __popc(a.y ^ f0.y) + __popc(a.z ^ f0.z) + __popc(a.w ^ f0.w) +
+                          __popc(b.x ^ f1.x) + __popc(b.y ^ f1.y) + __popc(b.z ^ f1.z) + __popc(b.w ^ f1.w);
+            if (d < best) { best = d; bi = c; } // if(d < best_d) (:1243)
+        }
+        cur = base + bi;
+        const int2 inf = __ldg(nodeInfo + cur);
+        base = inf.x;
+        cnt = inf.y;
+        if (level == nidLevel) nidNode = cur;
+    }
+    wordOut[f] = base;
+    weightOut[f] = __ldg(nodeWeight + cur);
+    nidOut[f] = __ldg(nodeOrig + (nidNode < 0 ? cur : nidNode));
 }
 
 // ---- BowVector / FeatureVector fold (transform(features, v, fv, levelsup), TemplatedVocabulary.h:1127-1190) ----
@@ -89,11 +147,13 @@ __device__ __forceinline__ void bitonic_sort_u64(unsigned long long *key, int np
 struct BowFoldParams {
     const int *word, *nid;   // per feature, all images back to back
     const double *weight;
-    const int *imgOff;       // [nimg + 1] prefix sums of the per-image feature counts
+    const int *imgOff;       // [nimg + 1] prefix sums of the per-image feature counts (packed batch, stride == 0)
+    const int *counts;       // strided batch: image i's features are rows i * stride .. + counts[i]
+    int stride;
     int tf, must, norm;      // weighting is TF / TF_IDF; scoring normalises; 1 = L1, 2 = L2
-    int *bowId;              // [total]: image i's entries at imgOff[i] .. + nBow[i]
+    int *bowId;              // image i's entries at its offset .. + nBow[i]
     double *bowVal;
-    unsigned long long *fvKey; // [total]: (node << 32 | feature index) ascending, image i's at imgOff[i] .. + nKept[i]
+    unsigned long long *fvKey; // [total]: (node << 32 | feature index) ascending, image i's at its offset .. + nKept[i]
     int *nBow, *nKept;       // [nimg]
 };
 
@@ -105,7 +165,8 @@ __global__ void __launch_bounds__(BF_THREADS) k_bow_fold(BowFoldParams P, int np
     __shared__ int scanTmp[34];
     __shared__ int sCount;
     __shared__ double sNorm;
-    const int img = blockIdx.x, off = P.imgOff[img], n = P.imgOff[img + 1] - off;
+    const int img = blockIdx.x, off = P.stride ? img * P.stride : P.imgOff[img];
+    const int n = P.stride ? min(P.counts[img], P.stride) : P.imgOff[img + 1] - off;
     const int *word = P.word + off, *nid = P.nid + off;
     const double *w = P.weight + off;
     if (threadIdx.x == 0) sCount = 0;

@@ -27,6 +27,7 @@ EXPORTS = [
     "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
     "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
     "orbb200_vocabulary_transform", "orbb200_vocabulary_transform_device", "orbb200_compute_bow_batch",
+    "orbb200_compute_bow_batch_device",
 ]
 
 _lib = None
@@ -88,6 +89,7 @@ def lib():
     L.orbb200_vocabulary_transform.argtypes = [vp, vp, ip, ip, vp, vp, vp]
     L.orbb200_vocabulary_transform_device.argtypes = [vp, vp, ip, ip, vp, vp, vp, vp]
     L.orbb200_compute_bow_batch.argtypes = [vp, vp, vp, ip, ip, vp, vp, vp, vp, vp, vp, vp]
+    L.orbb200_compute_bow_batch_device.argtypes = [vp, vp, vp, ip, ip, ip, vp, vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -404,6 +406,12 @@ class ORBVocabulary:
     def transform_features_device(self, desc_ptr, n, levelsup, word_ptr, weight_ptr, nid_ptr, stream=None):
         check(lib().orbb200_vocabulary_transform_device(self.h, C.c_void_p(desc_ptr), n, levelsup, C.c_void_p(word_ptr),
                                                         C.c_void_p(weight_ptr), C.c_void_p(nid_ptr), C.c_void_p(stream or 0)))
+
+    def compute_bow_batch_device(self, desc_ptr, n_ptr, nimg, cap, levelsup, bow_id_ptr, bow_val_ptr, n_bow_ptr, fv_key_ptr, n_kept_ptr,
+                                 stream=None):
+        check(lib().orbb200_compute_bow_batch_device(self.h, C.c_void_p(desc_ptr), C.c_void_p(n_ptr), nimg, cap, levelsup,
+                                                     C.c_void_p(bow_id_ptr), C.c_void_p(bow_val_ptr), C.c_void_p(n_bow_ptr),
+                                                     C.c_void_p(fv_key_ptr), C.c_void_p(n_kept_ptr), C.c_void_p(stream or 0)))
 
     def compute_bow_batch_raw(self, desc, counts, levelsup=4):
         desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)

@@ -50,3 +50,25 @@ def test_level_tables_host_logic_equals_oracle():
         assert t[4].sum() == nf
     assert L.orbb200_compute_level_tables(0, 1.2, 8, *[None] * 6) != 0
     assert b"bad parameters" in L.orbb200_last_error()
+
+
+def test_vocabulary_facade_scores_equal_reference(tmp_path):
+    """include/orbb200/ORBVocabulary.h::score -- host arithmetic, no device -- for all six DBoW2 scoring classes against
+    the reference's ScoringObject.cpp outputs (tests/golden/vocab_golden.npz, tools/make_vocab_golden.py)."""
+    import subprocess
+    import numpy as np
+    import vocab_cases as vc
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_vocab.bin")
+    assert os.path.exists(exe), "facade_vocab.bin not built: run __graft_entry__.build()"
+    for name in ("a", "b"):
+        files = []
+        for part in (0, 1):
+            bow, _ = vc.gold_maps("%s_w0_s0_l4" % name, part)
+            p = str(tmp_path / ("%s%d.txt" % (name, part)))
+            open(p, "w").write("".join("%d %s\n" % (k, float(v).hex()) for k, v in bow.items()))
+            files.append(p)
+        for sc in range(6):
+            r = subprocess.run([exe, "--score", str(sc)] + files, capture_output=True, text=True, timeout=60)
+            assert r.returncode == 0, r.stderr
+            got = [float.fromhex(x) for x in r.stdout.split()[1:3]]
+            assert got == list(vc.gold()["%s_scores6" % name][sc]), (name, sc, got)

@@ -90,3 +90,36 @@ def test_facade_matcher_templates_equal_reference_loops():
     assert os.path.exists(exe), "facade_match.bin not built: run __graft_entry__.build()"
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.count("ok ") == 16 and "FAIL" not in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("name,levelsup", [("a", 4), ("a", 2), ("b", 1), ("b", 4)])
+def test_facade_vocabulary_equals_reference_golden(tmp_path, name, levelsup):
+    """include/orbb200/ORBVocabulary.h driven like Frame::ComputeBoW / LoopClosing::DetectLoop, against the outputs of
+    the reference's own DBoW2 (tests/golden/vocab_golden.npz)."""
+    import vocab_cases as vc
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_vocab.bin")
+    assert os.path.exists(exe), "facade_vocab.bin not built: run __graft_entry__.build()"
+    g = vc.gold()
+    q = g["%s_queries" % name]
+    qp = str(tmp_path / "q.bin")
+    q.tofile(qp)
+    r = subprocess.run([exe, vc.vocab_path(name), qp, str(len(q)), str(levelsup), "300"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr + r.stdout
+    bow, fv, misc = {"A": {}, "B": {}}, {"A": {}, "B": {}}, {}
+    for line in r.stdout.splitlines():
+        t = line.split()
+        if t[0] in ("A", "B") and t[1] == "BOW":
+            bow[t[0]][int(t[2])] = float.fromhex(t[3])
+        elif t[0] in ("A", "B"):
+            fv[t[0]][int(t[2])] = [int(x) for x in t[3:]]
+        else:
+            misc[t[0]] = t[1:]
+    assert [int(x) for x in misc["INFO"][:3]] == [int(g["%s_info" % name][0]), int(g["%s_info" % name][1]), int(g["%s_info" % name][3])]
+    assert misc["BATCH"] == ["1"] and misc["EMPTY"] == ["1"]
+    for part, tag in enumerate(("A", "B")):
+        gb, gf = vc.gold_maps("%s_w0_s0_l%d" % (name, levelsup), part)
+        assert list(bow[tag].items()) == list(gb.items())
+        if vc.nid_defined(name, levelsup, *vc.PARTS[part]):
+            assert list(fv[tag].items()) == list(gf.items())
+    if levelsup == 4:
+        assert [float.fromhex(x) for x in misc["SCORE"]] == list(g["%s_w0_s0_score" % name])

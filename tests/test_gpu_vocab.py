@@ -50,14 +50,16 @@ def test_transform_equals_reference_golden(name, tmp_path):
                 assert list(fv.items()) == list(of.items())
 
 
-@pytest.mark.parametrize("k,L,p_stop,jit", [(10, 4, 0.0, False), (10, 5, 0.15, False), (16, 3, 0.0, True), (20, 3, 0.1, True),
-                                            (2, 10, 0.05, False), (3, 1, 0.0, False)])
-def test_transform_equals_oracle_on_synthetic_trees(k, L, p_stop, jit):
+@pytest.mark.parametrize("k,L,p_stop,jit,nq", [(10, 4, 0.0, False, 6000), (10, 5, 0.15, False, 6000), (16, 3, 0.0, True, 6000),
+                                               (20, 3, 0.1, True, 6000), (2, 10, 0.05, False, 6000), (3, 1, 0.0, False, 6000),
+                                               (10, 5, 0.15, False, 30000), (20, 3, 0.1, True, 30000), (2, 10, 0.05, False, 30000)])
+def test_transform_equals_oracle_on_synthetic_trees(k, L, p_stop, jit, nq):
+    """nq + 2000 features: below 16384 the lane-group mapping runs, above it the thread-per-feature mapping"""
     rng = np.random.default_rng(k * 100 + L)
     voc = vc.random_tree(rng, k, L, p_stop=p_stop, max_nodes=200000, k_jitter=jit)
     v = _from_oracle(voc)
     assert v.info()["nodes"] == voc.nnodes and v.size() == voc.nwords
-    q = np.concatenate([vc.queries_near_nodes(rng, voc, 6000), rng.integers(0, 256, (2000, 32), dtype=np.uint8)])
+    q = np.concatenate([vc.queries_near_nodes(rng, voc, nq), rng.integers(0, 256, (2000, 32), dtype=np.uint8)])
     for ls in (0, 2, L, L + 3):
         word, weight, nid = v.transform_features(q, ls)
         ow, owt, onid = vo.transform_features(voc, q, ls)
@@ -161,3 +163,47 @@ def test_transform_device_on_extracted_descriptors():
         assert n[i] == n_h[i] and n[i] > 500
         ow, owt, onid = vo.transform_features(voc, desc_h[i][:n[i]], 2)
         assert np.array_equal(word[i, :n[i]], ow) and np.array_equal(nid[i, :n[i]], onid) and np.array_equal(w[i, :n[i]], owt)
+
+
+def test_frame_front_end_resident_in_hbm():
+    """extraction -> ComputeBoW chained on one stream with device pointers only (orbb200_extract_batch_device ->
+    orbb200_compute_bow_batch_device): same maps as the host call on the downloaded descriptors"""
+    import torch
+    import synth
+    rng = np.random.default_rng(8)
+    voc = vc.random_tree(rng, 10, 4, p_stop=0.05)
+    v = _from_oracle(voc)
+    ex = orbb200.ORBextractor(1000, 1.2, 8, 20, 7)
+    B = 5
+    imgs = np.stack([synth.textured_frame(640, 480, 80 + i) for i in range(B)])
+    imgs[3] = 0                                                # a frame without keypoints
+    cap = ex.cap
+    _, desc_h, n_h = ex.extract_batch(imgs)
+    d_img = torch.from_numpy(imgs).cuda()
+    d_kps = torch.zeros(B * cap * 28, dtype=torch.uint8, device="cuda")
+    d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(B, dtype=torch.int32, device="cuda")
+    d_bid = torch.zeros((B, cap), dtype=torch.int32, device="cuda")
+    d_bval = torch.zeros((B, cap), dtype=torch.float64, device="cuda")
+    d_fkey = torch.zeros((B, cap), dtype=torch.int64, device="cuda")
+    d_nb = torch.zeros(B, dtype=torch.int32, device="cuda")
+    d_nk = torch.zeros(B, dtype=torch.int32, device="cuda")
+    ex.extract_batch_device(d_img.data_ptr(), B, 640, 480, 640, 640 * 480, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+    v.compute_bow_batch_device(d_desc.data_ptr(), d_n.data_ptr(), B, cap, 4, d_bid.data_ptr(), d_bval.data_ptr(), d_nb.data_ptr(),
+                               d_fkey.data_ptr(), d_nk.data_ptr(), ex.stream())
+    ex.sync()
+    n = d_n.cpu().numpy()
+    assert np.array_equal(n, n_h) and n[3] == 0
+    bid, bval, fkey = d_bid.cpu().numpy(), d_bval.cpu().numpy(), d_fkey.cpu().numpy().view(np.uint64)
+    nb, nk = d_nb.cpu().numpy(), d_nk.cpu().numpy()
+    host = v.compute_bow_batch(np.concatenate([desc_h[i][:n[i]] for i in range(B)]), n, 4)
+    for i in range(B):
+        bow, fv = host[i]
+        assert list(bow.keys()) == [int(x) for x in bid[i, :nb[i]]] and list(bow.values()) == [float(x) for x in bval[i, :nb[i]]]
+        keys = fkey[i, :nk[i]]
+        got = {}
+        for kx in keys:
+            got.setdefault(int(kx >> np.uint64(32)), []).append(int(kx & np.uint64(0xffffffff)))
+        assert list(got.items()) == list(fv.items())
+        ob, of = vo.transform(voc, desc_h[i][:n[i]], 4, per_feature=vo.transform_features(voc, desc_h[i][:n[i]], 4)) if n[i] else ({}, {})
+        assert list(bow.items()) == list(ob.items()) and list(fv.items()) == list(of.items())

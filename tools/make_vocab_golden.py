@@ -55,6 +55,8 @@ def main():
             assert r2.load_text(tmp)
             os.remove(tmp)
             info = r2.info()
+            if (wt, sc) == (0, 0):
+                r_l1 = r2
             out["%s_info" % name] = np.array([info["k"], info["L"], info["nodes"], info["words"]], np.int32)
             for ls in LEVELSUP:
                 tag = "%s_w%d_s%d_l%d" % (name, wt, sc, ls)
@@ -69,6 +71,17 @@ def main():
                 a = r2.transform(q[:300], 4)[0]
                 b = r2.transform(q[300:], 4)[0]
                 out["%s_w%d_s%d_score" % (name, wt, sc)] = np.array([r2.score(a, b), r2.score(a, a)], np.float64)
+        # the six scoring classes on the same two TF-IDF / L1 vectors (score(a, b) and score(b, a))
+        a, b = r_l1.transform(q[:300], 4)[0], r_l1.transform(q[300:], 4)[0]
+        sc6 = []
+        for sc in range(6):
+            tmp = os.path.join(GOLD, "_tmp_vocab.txt")
+            open(tmp, "w").write("\n".join(["%d %d %d %d" % (k, L, sc, 0)] + lines[1:]))
+            r2 = dbow2_ref.RefVocabulary()
+            assert r2.load_text(tmp)
+            os.remove(tmp)
+            sc6.append([r2.score(a, b), r2.score(b, a)])
+        out["%s_scores6" % name] = np.array(sc6, np.float64)
         print(name, info, "undefined nid at levelsup 0:", int((out["%s_w0_s0_l0_nid" % name] == -1).sum()))
     np.savez_compressed(os.path.join(GOLD, "vocab_golden.npz"), **out)
     print("wrote", len(out), "arrays")
