@@ -166,6 +166,19 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
 int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);
 int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream);
 
+/* replaces the arithmetic of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:266-340),
+ * batched over map points (callers: LocalMapping.cc:172,448,602,637; LoopClosing.cc:562; Tracking.cc:592,1232).
+ * Group g = the descriptors of the non-bad keyframes observing map point g, in the iteration order of
+ * mObservations (:288-294): rows [offsets[g], offsets[g+1]) of desc (32 bytes each), offsets[0] == 0.
+ * best_idx[g] = row (relative to the group) with the least median Hamming distance to the group, median =
+ * sorted row of Distances[i][*] (diagonal 0 included) at index (int)(0.5*(N-1)) (:327-331), first row wins ties
+ * (strict <, :333); -1 for an empty group (the reference returns early, :281,296).  best_median may be NULL. */
+int orbb200_distinctive_descriptors(const uint8_t *desc, const int *offsets, int ngroups, int *best_idx,
+                                    int *best_median, int device);
+/* the same with everything resident in HBM (desc_d 16-byte aligned), asynchronous on `stream` (NULL = internal) */
+int orbb200_distinctive_descriptors_device(const uint8_t *desc_d, const int *offsets_d, int ngroups, int *best_idx_d,
+                                           int *best_median_d, void *stream);
+
 /* F1: replaces Frame::ComputeStereoMatches (src/Frame.cc:577-751) using the device-resident pyramids and
  * outputs of the LAST single-image extract on `left` and `right`.  uRight[nL], depth[nL] host outputs
  * (-1 where unmatched).  bf = mbf, b = mb (baseline in metres). */

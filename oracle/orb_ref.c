@@ -776,6 +776,40 @@ int ref_ratio_accept(int best, int second, int th, float ratio)
     return best <= th && (float)best < ratio * (float)second;
 }
 
+/* MapPoint::ComputeDistinctiveDescriptors  src/MapPoint.cc:266-340, for a batch of map points (group g = the descriptors
+ * gathered at :288-294).  Distances[N][N] with a zero diagonal (:306-316), each row sorted (:329), median =
+ * vDists[0.5*(N-1)] (:331), strict < keeps the first row (:333-337).  Empty group: early return (:281,296) -> -1. */
+static int cmp_int(const void *a, const void *b) { return *(const int *)a - *(const int *)b; }
+void ref_distinctive_descriptors(const uint8_t *desc, const int *offsets, int ngroups, int *best_idx, int *best_median)
+{
+    for (int g = 0; g < ngroups; g++) {
+        const uint8_t *d = desc + (size_t)offsets[g] * 32;
+        const int N = offsets[g + 1] - offsets[g];
+        if (N <= 0) { best_idx[g] = -1; best_median[g] = 0; continue; }
+        float *D = (float *)malloc(sizeof(float) * (size_t)N * N); /* float like the reference's Distances[N][N] */
+        int *v = (int *)malloc(sizeof(int) * (size_t)N);
+        for (int i = 0; i < N; i++) {
+            D[(size_t)i * N + i] = 0;
+            for (int j = i + 1; j < N; j++) {
+                const int dij = ref_descriptor_distance(d + 32 * (size_t)i, d + 32 * (size_t)j);
+                D[(size_t)i * N + j] = (float)dij;
+                D[(size_t)j * N + i] = (float)dij;
+            }
+        }
+        int BestMedian = 0x7fffffff, BestIdx = 0;
+        for (int i = 0; i < N; i++) {
+            for (int j = 0; j < N; j++) v[j] = (int)D[(size_t)i * N + j]; /* vector<int> vDists(Distances[i], ...) */
+            qsort(v, (size_t)N, sizeof(int), cmp_int);
+            const int median = v[(int)(0.5 * (N - 1))];
+            if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+        }
+        best_idx[g] = BestIdx;
+        best_median[g] = BestMedian;
+        free(D);
+        free(v);
+    }
+}
+
 /* F3  Frame::AssignFeaturesToGrid + PosInGrid  src/Frame.cc:261-279, 444-456.
  * CSR over cells, cell id = ix*rows + iy (mGrid[ix][iy]), insertion (keypoint-index) order inside a cell */
 void ref_assign_grid(const ref_keypoint *kp, int n, float minX, float minY, float invW, float invH, int cols, int rows,

@@ -63,6 +63,7 @@ def lib():
     L.ref_bf_top2.argtypes = [vp, ip, vp, ip, vp, ip]
     L.ref_match_candidates.argtypes = [vp, ip, vp, vp, vp, vp]
     L.ref_ratio_accept.restype = ip
+    L.ref_distinctive_descriptors.argtypes = [vp, vp, ip, vp, vp]
     L.ref_ratio_accept.argtypes = [ip, ip, ip, fp]
     L.ref_assign_grid.argtypes = [vp, ip, fp, fp, fp, fp, ip, ip, vp, vp]
     L.ref_features_in_area.restype = ip
@@ -186,6 +187,17 @@ def match_candidates(q, t, offs, idx):
     out = np.zeros(len(q), TOP2_DTYPE)
     lib().ref_match_candidates(_p(q), len(q), _p(t), _p(offs), _p(idx), _p(out))
     return out
+
+
+def distinctive_descriptors(desc, offsets):
+    """MapPoint::ComputeDistinctiveDescriptors for a batch of groups -> (best row per group, its median)"""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    g = len(offsets) - 1
+    idx = np.zeros(g, np.int32)
+    med = np.zeros(g, np.int32)
+    lib().ref_distinctive_descriptors(_p(desc), _p(offsets), g, _p(idx), _p(med))
+    return idx, med
 
 
 def assign_grid(kps, minX, minY, invW, invH, cols=64, rows=48):

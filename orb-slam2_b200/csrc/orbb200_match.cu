@@ -4,6 +4,7 @@
 #include <algorithm>
 
 #include "extractor_host.cuh"
+#include "distinct_kernel.cuh"
 #include "match_kernels.cuh"
 #include "stereo_kernel.cuh"
 #include "window_kernels.cuh"
@@ -261,6 +262,48 @@ int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_t
     ORB_CUDA_OK(cudaMemcpyAsync(dp, parts, nb, cudaMemcpyHostToDevice, st));
     k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>((const orbb200_top2 *)dp, nshards, nq, (orbb200_top2 *)dout);
     ORB_CUDA_OK(cudaMemcpyAsync(out, dout, sizeof(orbb200_top2) * (size_t)nq, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_distinctive_descriptors_device(const uint8_t *desc_d, const int *offsets_d, int ngroups, int *best_idx_d,
+                                           int *best_median_d, void *stream)
+{
+    if (ngroups <= 0) return ORBB200_OK;
+    ORB_ARG_OK(desc_d && offsets_d && best_idx_d && best_median_d, "null pointer");
+    ORB_ARG_OK(((size_t)desc_d & 15) == 0, "descriptor array must be 16-byte aligned");
+    int rc = scratch_bind(-1);
+    if (rc) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_scratch.stream;
+    k_distinctive<<<div_up(ngroups, DD_WARPS), DD_WARPS * 32, 0, st>>>((const uint4 *)desc_d, offsets_d, ngroups, best_idx_d,
+                                                                      best_median_d);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
+}
+
+int orbb200_distinctive_descriptors(const uint8_t *desc, const int *offsets, int ngroups, int *best_idx, int *best_median,
+                                    int device)
+{
+    if (ngroups <= 0) return ORBB200_OK;
+    ORB_ARG_OK(offsets && best_idx, "null pointer");
+    ORB_ARG_OK(offsets[0] == 0, "offsets[0] must be 0");
+    for (int g = 0; g < ngroups; g++) ORB_ARG_OK(offsets[g + 1] >= offsets[g], "offsets must not decrease");
+    const int total = offsets[ngroups];
+    ORB_ARG_OK(total == 0 || desc, "null descriptors");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dd, *doffs, *dout;
+    if ((rc = scratch_get(0, (size_t)std::max(total, 1) * 32, &dd)) || (rc = scratch_get(3, (size_t)(ngroups + 1) * 4, &doffs)) ||
+        (rc = scratch_get(2, (size_t)ngroups * 8, &dout)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    if (total > 0) ORB_CUDA_OK(cudaMemcpyAsync(dd, desc, (size_t)total * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(doffs, offsets, (size_t)(ngroups + 1) * 4, cudaMemcpyHostToDevice, st));
+    k_distinctive<<<div_up(ngroups, DD_WARPS), DD_WARPS * 32, 0, st>>>((const uint4 *)dd, (const int *)doffs, ngroups, (int *)dout,
+                                                                      (int *)dout + ngroups);
+    ORB_CUDA_OK(cudaMemcpyAsync(best_idx, dout, (size_t)ngroups * 4, cudaMemcpyDeviceToHost, st));
+    if (best_median)
+        ORB_CUDA_OK(cudaMemcpyAsync(best_median, (int *)dout + ngroups, (size_t)ngroups * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_OK(cudaStreamSynchronize(st));
     return ORBB200_OK;
 }

@@ -27,7 +27,7 @@ EXPORTS = [
     "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
     "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
     "orbb200_vocabulary_transform", "orbb200_vocabulary_transform_device", "orbb200_compute_bow_batch",
-    "orbb200_compute_bow_batch_device",
+    "orbb200_compute_bow_batch_device", "orbb200_distinctive_descriptors", "orbb200_distinctive_descriptors_device",
 ]
 
 _lib = None
@@ -76,6 +76,8 @@ def lib():
     L.orbb200_window_search.argtypes = [vp, vp, ip, fp, fp, fp, fp, ip, ip, vp, vp, ip, vp, vp, vp, ip, ip]
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
+    L.orbb200_distinctive_descriptors.argtypes = [vp, vp, ip, vp, vp, ip]
+    L.orbb200_distinctive_descriptors_device.argtypes = [vp, vp, ip, vp, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
     L.orbb200_stereo_match_batch.argtypes = [vp, ip, fp, fp, vp, vp, vp]
     L.orbb200_stereo_match_batch_device.argtypes = [vp, ip, fp, fp, vp, vp, vp]
@@ -335,6 +337,17 @@ class ORBmatcher:
         out = np.zeros(nq, TOP2_DTYPE)
         check(self.L.orbb200_merge_top2(_p(parts), ns, nq, _p(out), self.device))
         return out
+
+    def distinctive_descriptors(self, desc, offsets):
+        """MapPoint::ComputeDistinctiveDescriptors (reference MapPoint.cc:266-340) for a batch of map points:
+        desc [total, 32] u8, offsets [G+1] -> (best row per group relative to the group, its median distance)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        g = len(offsets) - 1
+        idx = np.zeros(max(g, 0), np.int32)
+        med = np.zeros(max(g, 0), np.int32)
+        check(self.L.orbb200_distinctive_descriptors(_p(desc), _p(offsets), g, _p(idx), _p(med), self.device))
+        return idx, med
 
     def accept_ratio(self, top2, th=None):
         """best <= th and best < ratio*second (reference ORBmatcher.cc:242-244), f32 compare."""

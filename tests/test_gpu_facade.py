@@ -123,3 +123,14 @@ def test_facade_vocabulary_equals_reference_golden(tmp_path, name, levelsup):
             assert list(fv[tag].items()) == list(gf.items())
     if levelsup == 4:
         assert [float.fromhex(x) for x in misc["SCORE"]] == list(g["%s_w0_s0_score" % name])
+
+
+@pytest.mark.parametrize("seed,nkf,nmp", [(1, 6, 40), (2, 60, 1500)])
+def test_facade_distinctive_descriptors_equals_reference_loop(seed, nkf, nmp):
+    """include/orbb200/MapPointDescriptors.h: one device call for a keyframe's map points against
+    MapPoint::ComputeDistinctiveDescriptors written out statement for statement on stand-in types."""
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_distinct.bin")
+    assert os.path.exists(exe), "facade_distinct.bin not built: run __graft_entry__.build()"
+    r = subprocess.run([exe, str(seed), str(nkf), str(nmp)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
+    assert int(r.stdout.split()[2]) > nmp // 2

@@ -188,3 +188,27 @@ def test_fused_extract_stereo_equals_two_calls(configs):
         for p in range(P):
             nl_ = n[2 * p]
             assert np.array_equal(uR[p, :nl_], uR0[p, :nl_]) and np.array_equal(dep[p, :nl_], dep0[p, :nl_]), (chunk, ns, p)
+
+
+@pytest.mark.parametrize("name", ["small", "ragged_with_empty", "large", "ties"])
+def test_distinctive_descriptors_equals_oracle(name):
+    """MapPoint::ComputeDistinctiveDescriptors batched over map points: selected row and its median bit-exact"""
+    import distinct_cases as dc
+    desc, offs = dc.case(name)
+    gi, gm = orbb200.ORBmatcher().distinctive_descriptors(desc, offs)
+    ri, rm = ref_cpu.distinctive_descriptors(desc, offs)
+    assert np.array_equal(gi, ri), np.flatnonzero(gi != ri)[:8]
+    assert np.array_equal(gm, rm)
+
+
+def test_distinctive_descriptors_keyframe_sized_batch():
+    """a keyframe's worth of map points (2000 groups of 2..40 observations): equals the oracle; the selected row's median
+    is the minimum over its group (size-independent property)"""
+    import distinct_cases as dc
+    rng = np.random.default_rng(77)
+    sizes = rng.integers(2, 41, 2000).tolist()
+    desc, offs = dc.groups(78, sizes)
+    gi, gm = orbb200.ORBmatcher().distinctive_descriptors(desc, offs)
+    ri, rm = ref_cpu.distinctive_descriptors(desc, offs)
+    assert np.array_equal(gi, ri) and np.array_equal(gm, rm)
+    assert (gi >= 0).all() and (gi < np.diff(offs)).all()
