@@ -166,6 +166,26 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
 int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);
 int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream);
 
+/* ---- config 5 on N GPUs of one box: database rows sharded over ranks, one process per GPU --------------------
+ * The exchange step is fused into the search kernel: the last block to finish a group of 512 queries folds the rank's
+ * partial results, stores the shard's top-2 straight into every peer's gather buffer over NVLink (CUDA-IPC mapped peer
+ * memory), publishes a release flag, waits for the peers' flags and folds the shards in rank (= database) order, which
+ * reproduces the first-seen tie-break of the sequential loop (src/ORBmatcher.cc:229-235).  No NCCL on the data path;
+ * the 64-byte IPC handles travel through whatever the host uses for rendezvous (torch.distributed all_gather here).
+ *   create:  allocates the rank's exchange region, returns its IPC handle in ipc_handle_out[ORBB200_IPC_HANDLE_BYTES]
+ *   connect: all_handles = world handles in rank order (every rank's create has returned before any connect)
+ *   match:   asynchronous on `stream` (NULL = the exchange's own); EVERY rank must call it the same number of times with
+ *            the same nq; index_offset = global index of the rank's first row; out_d[nq] on every rank = the global top-2
+ *   status:  synchronises `stream`; ORBB200_ERR_CUDA when a peer failed to deliver within 10 s (no hang) */
+#define ORBB200_IPC_HANDLE_BYTES 64
+typedef struct orbb200_exchange orbb200_exchange;
+int orbb200_exchange_create(orbb200_exchange **out, int rank, int world, int nq_max, int device, void *ipc_handle_out);
+int orbb200_exchange_connect(orbb200_exchange *x, const void *all_handles);
+void orbb200_exchange_destroy(orbb200_exchange *x);
+int orbb200_match_sharded_top2_device(orbb200_exchange *x, const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb_local,
+                                      int index_offset, orbb200_top2 *out_d, void *stream);
+int orbb200_exchange_status(orbb200_exchange *x, void *stream);
+
 /* replaces the arithmetic of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:266-340),
  * batched over map points (callers: LocalMapping.cc:172,448,602,637; LoopClosing.cc:562; Tracking.cc:592,1232).
  * Group g = the descriptors of the non-bad keyframes observing map point g, in the iteration order of

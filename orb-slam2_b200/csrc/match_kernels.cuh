@@ -101,9 +101,126 @@ __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
 
+// ---- config 5 on N GPUs: the exchange step fused into the search kernel -------------------------------
+// Every rank owns a contiguous slice of database rows.  The LAST block to finish a query group (512 queries) folds that
+// group's per-chunk partials into the rank's shard result, stores it straight into every peer's gather buffer over
+// NVLink (cudaIpc-mapped peer memory, 16-byte stores), publishes one release flag per (rank, group) on every peer, waits
+// for the peers' flags of the same group and folds the world's shard results in rank order (= database order, so the
+// lexicographic (distance, index) rule is the sequential first-seen rule).  One launch per step, no NCCL call; groups
+// that finish early are exchanged while the other blocks are still searching.
+constexpr int EX_MAX_WORLD = 16;
+struct ExchangeParams {
+    int world, rank, epoch, nqMax, maxGroups; // epoch: 1, 2, 3, ... identical on every rank
+    int *groupCounter;                        // [maxGroups] local arrival counters (reset by the last block)
+    int *status;                              // [1] local: set to 1 when a peer's flag did not arrive in time
+    orbb200_top2 *out;                        // [nq] local result
+    // per rank p: its exchange region = gather [2][world][nqMax] records, then flags [world][maxGroups]
+    unsigned char *peer[EX_MAX_WORLD];
+    long long timeoutNs;
+};
+
+__device__ __forceinline__ orbb200_top2 *ex_gather(unsigned char *base, const ExchangeParams &X, int parity, int src)
+{
+    return reinterpret_cast<orbb200_top2 *>(base) + ((size_t)parity * X.world + src) * X.nqMax;
+}
+__device__ __forceinline__ int *ex_flags(unsigned char *base, const ExchangeParams &X)
+{
+    return reinterpret_cast<int *>(base + sizeof(orbb200_top2) * 2 * (size_t)X.world * X.nqMax);
+}
+__device__ __forceinline__ void st_release_sys(int *p, int v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ int ld_acquire_sys(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ long long global_ns()
+{
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ Top2 ex_load(const orbb200_top2 *p)
+{
+    const int4 v = __ldcg(reinterpret_cast<const int4 *>(p)); // written by other blocks / other GPUs: read at L2
+    Top2 t;
+    t.d1 = v.x; t.i1 = v.y; t.d2 = v.z; t.i2 = v.w;
+    return t;
+}
+
+__device__ __noinline__ void bf_exchange_tail(const ExchangeParams &X, const orbb200_top2 *partial, int nq, int q0, int nchunks)
+{
+    __shared__ int sLast;
+    const int g = blockIdx.x;
+    __threadfence(); // this block's partials are visible at L2 before its arrival is counted
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int prev = atomicAdd(&X.groupCounter[g], 1);
+        sLast = prev == nchunks - 1;
+        if (sLast) X.groupCounter[g] = 0; // every block of the group has arrived: ready for the next step
+    }
+    __syncthreads();
+    if (!sLast) return;
+    __threadfence();
+    // (1) this rank's shard result for the thread's BF_QPT queries: fold the chunks in database order
+    Top2 T[BF_QPT];
+#pragma unroll
+    for (int k = 0; k < BF_QPT; k++) top2_init(T[k]);
+    for (int c0 = 0; c0 < nchunks; c0 += 4) {
+        Top2 U[4][BF_QPT];
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+            for (int k = 0; k < BF_QPT; k++) {
+                if (c0 + j < nchunks && q0 + k < nq) U[j][k] = ex_load(partial + (size_t)(c0 + j) * nq + q0 + k);
+                else top2_init(U[j][k]);
+            }
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+            for (int k = 0; k < BF_QPT; k++) T[k] = top2_merge(T[k], U[j][k]);
+    }
+    // (2) 16-byte stores into every rank's gather buffer (own included), slot [epoch parity][this rank][query]
+    const int parity = X.epoch & 1;
+    for (int p = 0; p < X.world; p++) {
+        orbb200_top2 *dst = ex_gather(X.peer[p], X, parity, X.rank);
+#pragma unroll
+        for (int k = 0; k < BF_QPT; k++)
+            if (q0 + k < nq) *reinterpret_cast<int4 *>(dst + q0 + k) = make_int4(T[k].d1, T[k].i1, T[k].d2, T[k].i2);
+    }
+    __syncthreads();
+    // (3) publish: one release store per peer, after a system-scope fence that covers the whole block's stores
+    if (threadIdx.x == 0) __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < X.world) st_release_sys(ex_flags(X.peer[threadIdx.x], X) + X.rank * X.maxGroups + g, X.epoch);
+    // (4) wait for the same group of every rank (bounded: a missing peer becomes an error, not a hang)
+    if (threadIdx.x < X.world) {
+        const int *f = ex_flags(X.peer[X.rank], X) + threadIdx.x * X.maxGroups + g;
+        const long long t0 = global_ns();
+        while (ld_acquire_sys(f) < X.epoch) {
+            if (global_ns() - t0 > X.timeoutNs) { atomicExch(X.status, 1); break; }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+    // (5) fold the world's shard results in rank order
+#pragma unroll
+    for (int k = 0; k < BF_QPT; k++) top2_init(T[k]);
+    for (int s = 0; s < X.world; s++) {
+        const orbb200_top2 *src = ex_gather(X.peer[X.rank], X, parity, s);
+#pragma unroll
+        for (int k = 0; k < BF_QPT; k++)
+            if (q0 + k < nq) T[k] = top2_merge(T[k], ex_load(src + q0 + k));
+    }
+#pragma unroll
+    for (int k = 0; k < BF_QPT; k++)
+        if (q0 + k < nq) *reinterpret_cast<int4 *>(X.out + q0 + k) = make_int4(T[k].d1, T[k].i1, T[k].d2, T[k].i2);
+}
+
+template <bool EXCHANGE>
 __global__ void __launch_bounds__(BF_THREADS) k_bf_top2(const uint8_t *__restrict__ q, int nq, const uint8_t *__restrict__ db,
-                                                        int ndb, int rowsPerChunk, int indexOffset,
-                                                        orbb200_top2 *__restrict__ partial)
+                                                          int ndb, int rowsPerChunk, int indexOffset,
+                                                          orbb200_top2 *__restrict__ partial, const ExchangeParams X)
 {
     __shared__ __align__(16) uint4 tile[2][BF_TILE * 2];
     const int q0 = (blockIdx.x * BF_THREADS + threadIdx.x) * BF_QPT;
@@ -149,6 +266,7 @@ __global__ void __launch_bounds__(BF_THREADS) k_bf_top2(const uint8_t *__restric
             o.best_dist = T[k].d1; o.best_idx = T[k].i1; o.second_dist = T[k].d2; o.second_idx = T[k].i2;
             partial[(size_t)blockIdx.y * nq + q0 + k] = o;
         }
+    if (EXCHANGE) bf_exchange_tail(X, partial, nq, q0, (int)gridDim.y);
 }
 
 // fold nshards partial results per query; shards are ordered by database position, so the lexicographic

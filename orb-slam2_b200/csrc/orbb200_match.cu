@@ -67,13 +67,27 @@ static int bf_launch(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, o
     void *partial;
     int rc = scratch_get(5, sizeof(orbb200_top2) * (size_t)chunks * nq, &partial);
     if (rc) return rc;
-    k_bf_top2<<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb, rows, indexOffset, (orbb200_top2 *)partial);
+    k_bf_top2<false><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb, rows, indexOffset, (orbb200_top2 *)partial,
+                                                                  ExchangeParams());
     k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>((const orbb200_top2 *)partial, chunks, nq, out_d);
     ORB_CUDA_OK(cudaGetLastError());
     return ORBB200_OK;
 }
 
 } // namespace orbb200
+
+// config 5 on N GPUs: one exchange region per rank (gather slots + flags), mapped into every peer with CUDA IPC
+struct orbb200_exchange {
+    int rank = 0, world = 1, nqMax = 0, maxGroups = 0, device = 0, epoch = 0;
+    bool connected = false;
+    unsigned char *region = nullptr; // own region
+    size_t regionBytes = 0;
+    int *groupCounter = nullptr, *status = nullptr;
+    unsigned char *peer[orbb200::EX_MAX_WORLD] = {};
+    cudaStream_t stream = nullptr;
+    void *partial = nullptr;
+    size_t partialCap = 0;
+};
 
 #include "stereo_host.inc"
 
@@ -305,6 +319,112 @@ int orbb200_distinctive_descriptors(const uint8_t *desc, const int *offsets, int
     if (best_median)
         ORB_CUDA_OK(cudaMemcpyAsync(best_median, (int *)dout + ngroups, (size_t)ngroups * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_exchange_create(orbb200_exchange **out, int rank, int world, int nq_max, int device, void *ipc_handle_out)
+{
+    ORB_ARG_OK(out && ipc_handle_out, "null pointer");
+    ORB_ARG_OK(world >= 1 && world <= EX_MAX_WORLD && rank >= 0 && rank < world && nq_max > 0, "bad rank / world / nq_max");
+    static_assert(sizeof(cudaIpcMemHandle_t) == ORBB200_IPC_HANDLE_BYTES, "IPC handle size");
+    if (device < 0) ORB_CUDA_OK(cudaGetDevice(&device));
+    ORB_CUDA_OK(cudaSetDevice(device));
+    orbb200_exchange *x = new orbb200_exchange();
+    x->rank = rank; x->world = world; x->device = device;
+    x->nqMax = (int)align_up((size_t)nq_max, BF_THREADS * BF_QPT);
+    x->maxGroups = x->nqMax / (BF_THREADS * BF_QPT);
+    x->regionBytes = align_up(sizeof(orbb200_top2) * 2 * (size_t)world * x->nqMax + sizeof(int) * (size_t)world * x->maxGroups, 256);
+    cudaError_t e = cudaMalloc(&x->region, x->regionBytes);
+    if (e == cudaSuccess) e = cudaMemset(x->region, 0, x->regionBytes);
+    if (e == cudaSuccess) e = cudaMalloc(&x->groupCounter, sizeof(int) * (size_t)(x->maxGroups + 1));
+    if (e == cudaSuccess) e = cudaMemset(x->groupCounter, 0, sizeof(int) * (size_t)(x->maxGroups + 1));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle((cudaIpcMemHandle_t *)ipc_handle_out, x->region);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize(); // the zeroed flags are in place before any peer can map the region
+    if (e != cudaSuccess) {
+        set_error("orbb200_exchange_create: %s", cudaGetErrorString(e));
+        orbb200_exchange_destroy(x);
+        return ORBB200_ERR_CUDA;
+    }
+    x->status = x->groupCounter + x->maxGroups;
+    x->peer[rank] = x->region;
+    x->connected = world == 1;
+    *out = x;
+    return ORBB200_OK;
+}
+
+int orbb200_exchange_connect(orbb200_exchange *x, const void *all_handles)
+{
+    ORB_ARG_OK(x && all_handles, "null pointer");
+    ORB_CUDA_OK(cudaSetDevice(x->device));
+    const cudaIpcMemHandle_t *h = (const cudaIpcMemHandle_t *)all_handles;
+    for (int p = 0; p < x->world; p++) {
+        if (p == x->rank || x->peer[p]) continue;
+        void *ptr = nullptr;
+        ORB_CUDA_OK(cudaIpcOpenMemHandle(&ptr, h[p], cudaIpcMemLazyEnablePeerAccess));
+        x->peer[p] = (unsigned char *)ptr;
+    }
+    x->connected = true;
+    return ORBB200_OK;
+}
+
+void orbb200_exchange_destroy(orbb200_exchange *x)
+{
+    if (!x) return;
+    cudaSetDevice(x->device);
+    if (x->stream) cudaStreamSynchronize(x->stream);
+    for (int p = 0; p < x->world; p++)
+        if (p != x->rank && x->peer[p]) cudaIpcCloseMemHandle(x->peer[p]);
+    if (x->region) cudaFree(x->region);
+    if (x->groupCounter) cudaFree(x->groupCounter);
+    if (x->partial) cudaFree(x->partial);
+    if (x->stream) cudaStreamDestroy(x->stream);
+    delete x;
+}
+
+int orbb200_match_sharded_top2_device(orbb200_exchange *x, const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb_local,
+                                      int index_offset, orbb200_top2 *out_d, void *stream)
+{
+    ORB_ARG_OK(x && q_d && db_d && out_d && nq > 0 && ndb_local > 0, "bad arguments");
+    ORB_ARG_OK(x->connected, "orbb200_exchange_connect has not been called");
+    ORB_ARG_OK(nq <= x->nqMax, "nq exceeds the exchange's nq_max");
+    ORB_ARG_OK(((size_t)q_d & 15) == 0 && ((size_t)db_d & 15) == 0 && ((size_t)out_d & 15) == 0, "arrays must be 16-byte aligned");
+    ORB_CUDA_OK(cudaSetDevice(x->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    int groups, chunks, rows;
+    bf_plan(nq, ndb_local, &groups, &chunks, &rows);
+    const size_t need = sizeof(orbb200_top2) * (size_t)chunks * nq;
+    if (x->partialCap < need) {
+        ORB_CUDA_OK(cudaStreamSynchronize(st));
+        if (x->partial) cudaFree(x->partial);
+        x->partial = nullptr; x->partialCap = 0;
+        ORB_CUDA_OK(cudaMalloc(&x->partial, align_up(need, 256)));
+        x->partialCap = align_up(need, 256);
+    }
+    ExchangeParams X;
+    memset(&X, 0, sizeof(X));
+    X.world = x->world; X.rank = x->rank; X.epoch = ++x->epoch; X.nqMax = x->nqMax; X.maxGroups = x->maxGroups;
+    X.groupCounter = x->groupCounter; X.status = x->status; X.out = out_d;
+    for (int p = 0; p < x->world; p++) X.peer[p] = x->peer[p];
+    X.timeoutNs = 10LL * 1000 * 1000 * 1000;
+    k_bf_top2<true><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb_local, rows, index_offset,
+                                                                (orbb200_top2 *)x->partial, X);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
+}
+
+int orbb200_exchange_status(orbb200_exchange *x, void *stream)
+{
+    ORB_ARG_OK(x != nullptr, "null pointer");
+    ORB_CUDA_OK(cudaSetDevice(x->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    int s = 0;
+    ORB_CUDA_OK(cudaMemcpyAsync(&s, x->status, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    if (s != 0) {
+        set_error("orbb200_match_sharded_top2_device: a peer's shard result did not arrive within the timeout");
+        return ORBB200_ERR_CUDA;
+    }
     return ORBB200_OK;
 }
 

@@ -28,6 +28,8 @@ EXPORTS = [
     "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
     "orbb200_vocabulary_transform", "orbb200_vocabulary_transform_device", "orbb200_compute_bow_batch",
     "orbb200_compute_bow_batch_device", "orbb200_distinctive_descriptors", "orbb200_distinctive_descriptors_device",
+    "orbb200_exchange_create", "orbb200_exchange_connect", "orbb200_exchange_destroy", "orbb200_match_sharded_top2_device",
+    "orbb200_exchange_status",
 ]
 
 _lib = None
@@ -77,6 +79,12 @@ def lib():
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_distinctive_descriptors.argtypes = [vp, vp, ip, vp, vp, ip]
+    L.orbb200_exchange_create.argtypes = [vp, ip, ip, ip, ip, vp]
+    L.orbb200_exchange_connect.argtypes = [vp, vp]
+    L.orbb200_exchange_destroy.argtypes = [vp]
+    L.orbb200_exchange_destroy.restype = None
+    L.orbb200_match_sharded_top2_device.argtypes = [vp, vp, ip, vp, ip, ip, vp, vp]
+    L.orbb200_exchange_status.argtypes = [vp, vp]
     L.orbb200_distinctive_descriptors_device.argtypes = [vp, vp, ip, vp, vp, vp]
     L.orbb200_stereo_match.argtypes = [vp, vp, fp, fp, vp, vp, vp]
     L.orbb200_stereo_match_batch.argtypes = [vp, ip, fp, fp, vp, vp, vp]
@@ -469,6 +477,39 @@ def stereo_match(left, right, bf, b):
 
 
 # ---- multi-GPU host logic: frames and database rows are sharded per rank --------------------------
+class ShardedMatcher:
+    """Config 5 on N GPUs (one process per GPU): brute-force top-2 over a row-sharded database with the exchange step
+    fused into the search kernel (peer stores over NVLink + flags, include/orbb200.h "config 5 on N GPUs").
+    The 64-byte IPC handles are all-gathered once through torch.distributed (host plumbing, any backend)."""
+    IPC_HANDLE_BYTES = 64
+
+    def __init__(self, rank, world, nq_max, device=-1, group=None):
+        self.L = lib()
+        self.h = C.c_void_p()
+        self.rank, self.world = rank, world
+        handle = np.zeros(self.IPC_HANDLE_BYTES, np.uint8)
+        check(self.L.orbb200_exchange_create(C.byref(self.h), rank, world, nq_max, device, _p(handle)))
+        if world > 1:
+            import torch.distributed as dist
+            gathered = [None] * world
+            dist.all_gather_object(gathered, handle.tobytes(), group=group)  # also orders every create before any connect
+            allh = np.frombuffer(b"".join(gathered), np.uint8).copy()
+            check(self.L.orbb200_exchange_connect(self.h, _p(allh)))
+
+    def __del__(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.orbb200_exchange_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def match_device(self, q_ptr, nq, db_ptr, ndb_local, index_offset, out_ptr, stream=0):
+        """asynchronous; device pointers; every rank calls it the same number of times"""
+        check(self.L.orbb200_match_sharded_top2_device(self.h, C.c_void_p(q_ptr), nq, C.c_void_p(db_ptr), ndb_local, index_offset,
+                                                        C.c_void_p(out_ptr), C.c_void_p(stream)))
+
+    def status(self, stream=0):
+        check(self.L.orbb200_exchange_status(self.h, C.c_void_p(stream)))
+
+
 def shard_range(n, world, rank):
     """contiguous [lo, hi) slice of n units owned by `rank` of `world` (first n % world ranks get one more)"""
     base, rem = divmod(n, world)
