@@ -119,6 +119,29 @@ int orbb200_extractor_last_launches(const orbb200_extractor *e);
 int orbb200_debug_candidates(orbb200_extractor *e, int image_index, int level, int *xyr, int cap, int *n);
 int orbb200_debug_blurred_level(orbb200_extractor *e, int image_index, int level, uint8_t *dst, int dst_stride);
 
+/* ---- prologue of the path -------------------------------------------------------------------
+ * Colour input: Tracking::GrabImageStereo / RGBD / Monocular convert with cv::cvtColor(im, gray, CV_RGB2GRAY | CV_BGR2GRAY |
+ * CV_RGBA2GRAY | CV_BGRA2GRAY) (src/Tracking.cc:177-202, 218-231, 255-266) before building the Frame.  Here the conversion
+ * is fused into the level-0 staging of the extraction: interleaved `channels` (3 or 4) bytes per pixel in, r_first != 0 when
+ * channel 0 is red (mbRGB).  gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, bit-exact with OpenCV's 8-bit path; the
+ * gray image (mImGray) is level 0 of the pyramid: orbb200_pyramid_level(e, image, 0, ...). */
+int orbb200_extract_color(orbb200_extractor *e, const uint8_t *img, int width, int height, int stride, int channels,
+                          int r_first, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out);
+int orbb200_extract_color_batch(orbb200_extractor *e, const uint8_t *const *imgs, int batch, int width, int height,
+                                int stride, int channels, int r_first, orbb200_keypoint *kps, uint8_t *desc, int cap,
+                                int *n_out);
+/* the conversion alone (host buffers) */
+int orbb200_cvt_gray(const uint8_t *img, int width, int height, int stride, int channels, int r_first, uint8_t *gray,
+                     int gray_stride, int device);
+/* replaces Frame::UndistortKeyPoints (src/Frame.cc:470-515) = cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK);
+ * also serves the four corners of Frame::ComputeImageBounds (:517-550).  cam = {fx, fy, cx, cy} of mK and
+ * dist_coef = {k1, k2, p1, p2, k3} of mDistCoef as the reference stores them (float).  k1 == 0 copies (:473-477).
+ * Only x, y change; double arithmetic, 5 iterations, bit-exact with OpenCV.  out may alias kps. */
+int orbb200_undistort_keypoints(const orbb200_keypoint *kps, int n, const float *cam, const float *dist_coef,
+                                orbb200_keypoint *out, int device);
+int orbb200_undistort_keypoints_device(const orbb200_keypoint *kps_d, int n, const float *cam, const float *dist_coef,
+                                       orbb200_keypoint *out_d, void *stream);
+
 /* ---- matcher ---------------------------------------------------------------------------------------- */
 
 /* running best / second-best of ORBmatcher's searches (src/ORBmatcher.cc:214-240): best_idx is the first

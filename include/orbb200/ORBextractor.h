@@ -91,6 +91,40 @@ public:
         if (pyramidMode_ == PYRAMID_EAGER) download_pyramid();
     }
 
+    /* Extension: the cv::cvtColor prologue of Tracking::GrabImage* (src/Tracking.cc:177-202, 218-231, 255-266)
+     * fused into the extraction.  imColor is CV_8UC3 / CV_8UC4, bRGB = Tracking::mbRGB (channel 0 is red).  imGray receives
+     * what cvtColor would have produced (Tracking keeps it as mImGray) -- it is level 0 of the device pyramid. */
+    void ExtractColor(const cv::Mat &imColor, bool bRGB, std::vector<cv::KeyPoint> &_keypoints, cv::OutputArray _descriptors,
+                      cv::Mat *imGray = nullptr)
+    {
+        if (imColor.empty()) return;
+        _keypoints.clear();
+        const int ch = imColor.channels();
+        if (imColor.depth() != CV_8U || (ch != 3 && ch != 4)) { fail("colour image must be CV_8UC3 or CV_8UC4", _descriptors); return; }
+        if (!ensure_handle()) { fail(orbb200_last_error(), _descriptors); return; }
+        const int cap = orbb200_max_keypoints(handle_);
+        _keypoints.resize(cap);
+        descBuf_.resize((size_t)cap * 32);
+        int n = 0;
+        const int rc = orbb200_extract_color(handle_, imColor.data, imColor.cols, imColor.rows, (int)imColor.step, ch, bRGB ? 1 : 0,
+                                             reinterpret_cast<orbb200_keypoint *>(_keypoints.data()), descBuf_.data(), cap, &n);
+        if (rc != ORBB200_OK) { _keypoints.clear(); fail(orbb200_last_error(), _descriptors); return; }
+        _keypoints.resize(n);
+        if (n == 0) {
+            _descriptors.release();
+        } else {
+            _descriptors.create(n, 32, CV_8U);
+            cv::Mat d = _descriptors.getMat();
+            for (int i = 0; i < n; i++) std::memcpy(d.ptr(i), descBuf_.data() + (size_t)i * 32, 32);
+        }
+        if (pyramidMode_ == PYRAMID_EAGER) download_pyramid();
+        if (imGray) {
+            int w = 0, h = 0;
+            imGray->create(imColor.rows, imColor.cols, CV_8UC1);
+            orbb200_pyramid_level(handle_, 0, 0, imGray->data, (int)imGray->step, &w, &h);
+        }
+    }
+
     int inline GetLevels() { return nlevels; }
     float inline GetScaleFactor() { return (float)scaleFactor; }
     std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
@@ -168,6 +202,24 @@ inline int ComputeStereoMatches(ORB_SLAM2::ORBextractor &left, ORB_SLAM2::ORBext
     }
     for (int i = 0; i < nLeft && i < cap; i++) { mvuRight[i] = u[i]; mvDepth[i] = d[i]; }
     return nvalid;
+}
+
+/* Device replacement of Frame::UndistortKeyPoints (src/Frame.cc:470-515).  mK is the 3x3 CV_32F camera matrix, mDistCoef the
+ * 4x1 / 5x1 CV_32F coefficients (k1, k2, p1, p2[, k3]) exactly as Frame holds them; k1 == 0 copies (:473-477). */
+inline void UndistortKeyPoints(const std::vector<cv::KeyPoint> &mvKeys, const cv::Mat &mK, const cv::Mat &mDistCoef,
+                               std::vector<cv::KeyPoint> &mvKeysUn, int device = -1)
+{
+    const int nCoef = mDistCoef.rows * mDistCoef.cols;
+    float dist[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < nCoef && i < 5; i++) dist[i] = mDistCoef.ptr<float>()[i];
+    if (dist[0] == 0.0f || mvKeys.empty()) { mvKeysUn = mvKeys; return; }
+    const float cam[4] = {mK.at<float>(0, 0), mK.at<float>(1, 1), mK.at<float>(0, 2), mK.at<float>(1, 2)};
+    mvKeysUn.resize(mvKeys.size());
+    if (orbb200_undistort_keypoints(reinterpret_cast<const orbb200_keypoint *>(mvKeys.data()), (int)mvKeys.size(), cam, dist,
+                                    reinterpret_cast<orbb200_keypoint *>(mvKeysUn.data()), device) != ORBB200_OK) {
+        std::cerr << "UndistortKeyPoints (orbb200): " << orbb200_last_error() << std::endl;
+        mvKeysUn = mvKeys;
+    }
 }
 
 } // namespace orbb200

@@ -20,6 +20,9 @@
 #define CV_8UC1 0
 #define CV_32F 5
 #define CV_32FC1 5
+/* OpenCV's encoding: type = depth + ((channels - 1) << 3) */
+#define CV_8UC3 16
+#define CV_8UC4 24
 
 namespace cv {
 
@@ -72,7 +75,8 @@ public:
     size_t elemSize() const { return esz(type_); }
     bool isContinuous() const { return step == (size_t)cols * esz(type_); }
     Size size() const { return Size(cols, rows); }
-    int channels() const { return 1; }
+    int channels() const { return (type_ >> 3) + 1; }
+    int depth() const { return type_ & 7; }
 
     template <typename T> T *ptr(int r = 0) { return reinterpret_cast<T *>(data + (size_t)r * step); }
     template <typename T> const T *ptr(int r = 0) const { return reinterpret_cast<const T *>(data + (size_t)r * step); }
@@ -112,7 +116,7 @@ public:
     const Mat &getMat() const { return *this; } /* so `_image.getMat()` style code keeps compiling */
 
 private:
-    static size_t esz(int type) { return type == CV_32F ? 4 : 1; }
+    static size_t esz(int type) { return (size_t)((type & 7) == CV_32F ? 4 : 1) * (size_t)((type >> 3) + 1); }
     int type_;
     std::shared_ptr<unsigned char> store_;
 };

@@ -102,8 +102,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
 
 // ---- config 5 on N GPUs: the exchange step fused into the search kernel -------------------------------
-// Every rank owns a contiguous slice of database rows.  The LAST block to finish a query group (512 queries) folds that
-// group's per-chunk partials into the rank's shard result, stores it straight into every peer's gather buffer over
+// Every rank owns a contiguous slice of database rows.  Every block folds its chunk's top-2 into per-query accumulators
+// at L2 (two 64-bit atomicMin keys); the LAST block to finish a query group (512 queries) reads the group's shard result,
+// stores it straight into every peer's gather buffer over
 // NVLink (cudaIpc-mapped peer memory, 16-byte stores), publishes one release flag per (rank, group) on every peer, waits
 // for the peers' flags of the same group and folds the world's shard results in rank order (= database order, so the
 // lexicographic (distance, index) rule is the sequential first-seen rule).  One launch per step, no NCCL call; groups
@@ -112,6 +113,7 @@ constexpr int EX_MAX_WORLD = 16;
 struct ExchangeParams {
     int world, rank, epoch, nqMax, maxGroups; // epoch: 1, 2, 3, ... identical on every rank
     int *groupCounter;                        // [maxGroups] local arrival counters (reset by the last block)
+    unsigned long long *acc;                  // [nqMax][2] local per-query accumulators of the shard's top-2 (packed keys)
     int *status;                              // [1] local: set to 1 when a peer's flag did not arrive in time
     orbb200_top2 *out;                        // [nq] local result
     // per rank p: its exchange region = gather [2][world][nqMax] records, then flags [world][maxGroups]
@@ -148,11 +150,30 @@ __device__ __forceinline__ Top2 ex_load(const orbb200_top2 *p)
     return t;
 }
 
-__device__ __noinline__ void bf_exchange_tail(const ExchangeParams &X, const orbb200_top2 *partial, int nq, int q0, int nchunks)
+__device__ __forceinline__ unsigned long long ex_pack(int d, int i) { return ((unsigned long long)(unsigned int)d << 32) | (unsigned int)i; }
+constexpr unsigned long long EX_ABSENT = (256ull << 32) | 0xFFFFFFFFull; // (256, -1): sorts after every real candidate
+
+// Tail of k_bf_top2<true>.  T = the block's top-2 of its database chunk for the thread's BF_QPT queries.
+__device__ __forceinline__ void bf_exchange_tail(const ExchangeParams &X, const Top2 (&Tin)[BF_QPT], int nq, int q0, int nchunks)
 {
     __shared__ int sLast;
     const int g = blockIdx.x;
-    __threadfence(); // this block's partials are visible at L2 before its arrival is counted
+    // (0) fold the chunk result into the group's accumulators at L2: acc[q] = {smallest, second smallest} packed
+    //     (distance, global index) key.  64-bit atomicMin on key 1 returns what it displaced; the loser of that duel and
+    //     the chunk's own second both go to key 2 -- min is commutative, so the arrival order of the blocks is irrelevant
+    //     and the final pair is the two lexicographically smallest keys of the whole shard.
+#pragma unroll
+    for (int k = 0; k < BF_QPT; k++) {
+        if (q0 + k >= nq) continue;
+        unsigned long long *a = X.acc + 2 * (size_t)(q0 + k);
+        const unsigned long long k1 = ex_pack(Tin[k].d1, Tin[k].i1), k2 = ex_pack(Tin[k].d2, Tin[k].i2);
+        if (k1 == EX_ABSENT) continue;
+        const unsigned long long old = atomicMin(a, k1);
+        const unsigned long long loser = old > k1 ? old : k1;
+        if (loser != EX_ABSENT) atomicMin(a + 1, loser);
+        if (k2 != EX_ABSENT) atomicMin(a + 1, k2);
+    }
+    __threadfence(); // the atomics are performed before the arrival is counted
     __syncthreads();
     if (threadIdx.x == 0) {
         const int prev = atomicAdd(&X.groupCounter[g], 1);
@@ -162,23 +183,17 @@ __device__ __noinline__ void bf_exchange_tail(const ExchangeParams &X, const orb
     __syncthreads();
     if (!sLast) return;
     __threadfence();
-    // (1) this rank's shard result for the thread's BF_QPT queries: fold the chunks in database order
+    // (1) the last block reads the shard result and re-arms the accumulators for the next step
     Top2 T[BF_QPT];
 #pragma unroll
-    for (int k = 0; k < BF_QPT; k++) top2_init(T[k]);
-    for (int c0 = 0; c0 < nchunks; c0 += 4) {
-        Top2 U[4][BF_QPT];
-#pragma unroll
-        for (int j = 0; j < 4; j++)
-#pragma unroll
-            for (int k = 0; k < BF_QPT; k++) {
-                if (c0 + j < nchunks && q0 + k < nq) U[j][k] = ex_load(partial + (size_t)(c0 + j) * nq + q0 + k);
-                else top2_init(U[j][k]);
-            }
-#pragma unroll
-        for (int j = 0; j < 4; j++)
-#pragma unroll
-            for (int k = 0; k < BF_QPT; k++) T[k] = top2_merge(T[k], U[j][k]);
+    for (int k = 0; k < BF_QPT; k++) {
+        top2_init(T[k]);
+        if (q0 + k >= nq) continue;
+        ulonglong2 *a = reinterpret_cast<ulonglong2 *>(X.acc + 2 * (size_t)(q0 + k));
+        const ulonglong2 v = __ldcg(a);
+        T[k].d1 = (int)(v.x >> 32); T[k].i1 = (int)(unsigned int)v.x;
+        T[k].d2 = (int)(v.y >> 32); T[k].i2 = (int)(unsigned int)v.y;
+        *a = make_ulonglong2(EX_ABSENT, EX_ABSENT);
     }
     // (2) 16-byte stores into every rank's gather buffer (own included), slot [epoch parity][this rank][query]
     const int parity = X.epoch & 1;
@@ -199,7 +214,7 @@ __device__ __noinline__ void bf_exchange_tail(const ExchangeParams &X, const orb
         const long long t0 = global_ns();
         while (ld_acquire_sys(f) < X.epoch) {
             if (global_ns() - t0 > X.timeoutNs) { atomicExch(X.status, 1); break; }
-            __nanosleep(64);
+            __nanosleep(32);
         }
     }
     __syncthreads();
@@ -259,14 +274,17 @@ __global__ void __launch_bounds__(BF_THREADS) k_bf_top2(const uint8_t *__restric
         }
         __syncthreads();
     }
+    if constexpr (EXCHANGE) {
+        bf_exchange_tail(X, T, nq, q0, (int)gridDim.y);
+    } else {
 #pragma unroll
-    for (int k = 0; k < BF_QPT; k++)
-        if (q0 + k < nq) {
-            orbb200_top2 o;
-            o.best_dist = T[k].d1; o.best_idx = T[k].i1; o.second_dist = T[k].d2; o.second_idx = T[k].i2;
-            partial[(size_t)blockIdx.y * nq + q0 + k] = o;
-        }
-    if (EXCHANGE) bf_exchange_tail(X, partial, nq, q0, (int)gridDim.y);
+        for (int k = 0; k < BF_QPT; k++)
+            if (q0 + k < nq) {
+                orbb200_top2 o;
+                o.best_dist = T[k].d1; o.best_idx = T[k].i1; o.second_dist = T[k].d2; o.second_idx = T[k].i2;
+                partial[(size_t)blockIdx.y * nq + q0 + k] = o;
+            }
+    }
 }
 
 // fold nshards partial results per query; shards are ordered by database position, so the lexicographic

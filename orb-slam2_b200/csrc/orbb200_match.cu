@@ -2,6 +2,7 @@
 // Mirrors the arithmetic of ORB_SLAM2::ORBmatcher (reference src/ORBmatcher.cc) on POD arrays; the
 // MapPoint / KeyFrame bookkeeping of the Search* methods stays in the C++ facade (include/orbb200/ORBmatcher.h).
 #include <algorithm>
+#include <vector>
 
 #include "extractor_host.cuh"
 #include "distinct_kernel.cuh"
@@ -83,10 +84,9 @@ struct orbb200_exchange {
     unsigned char *region = nullptr; // own region
     size_t regionBytes = 0;
     int *groupCounter = nullptr, *status = nullptr;
+    unsigned long long *acc = nullptr;
     unsigned char *peer[orbb200::EX_MAX_WORLD] = {};
     cudaStream_t stream = nullptr;
-    void *partial = nullptr;
-    size_t partialCap = 0;
 };
 
 #include "stereo_host.inc"
@@ -338,6 +338,11 @@ int orbb200_exchange_create(orbb200_exchange **out, int rank, int world, int nq_
     if (e == cudaSuccess) e = cudaMemset(x->region, 0, x->regionBytes);
     if (e == cudaSuccess) e = cudaMalloc(&x->groupCounter, sizeof(int) * (size_t)(x->maxGroups + 1));
     if (e == cudaSuccess) e = cudaMemset(x->groupCounter, 0, sizeof(int) * (size_t)(x->maxGroups + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&x->acc, sizeof(unsigned long long) * 2 * (size_t)x->nqMax);
+    if (e == cudaSuccess) {
+        std::vector<unsigned long long> init(2 * (size_t)x->nqMax, EX_ABSENT);
+        e = cudaMemcpy(x->acc, init.data(), sizeof(unsigned long long) * init.size(), cudaMemcpyHostToDevice);
+    }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaIpcGetMemHandle((cudaIpcMemHandle_t *)ipc_handle_out, x->region);
     if (e == cudaSuccess) e = cudaDeviceSynchronize(); // the zeroed flags are in place before any peer can map the region
@@ -377,7 +382,7 @@ void orbb200_exchange_destroy(orbb200_exchange *x)
         if (p != x->rank && x->peer[p]) cudaIpcCloseMemHandle(x->peer[p]);
     if (x->region) cudaFree(x->region);
     if (x->groupCounter) cudaFree(x->groupCounter);
-    if (x->partial) cudaFree(x->partial);
+    if (x->acc) cudaFree(x->acc);
     if (x->stream) cudaStreamDestroy(x->stream);
     delete x;
 }
@@ -393,22 +398,13 @@ int orbb200_match_sharded_top2_device(orbb200_exchange *x, const uint8_t *q_d, i
     cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
     int groups, chunks, rows;
     bf_plan(nq, ndb_local, &groups, &chunks, &rows);
-    const size_t need = sizeof(orbb200_top2) * (size_t)chunks * nq;
-    if (x->partialCap < need) {
-        ORB_CUDA_OK(cudaStreamSynchronize(st));
-        if (x->partial) cudaFree(x->partial);
-        x->partial = nullptr; x->partialCap = 0;
-        ORB_CUDA_OK(cudaMalloc(&x->partial, align_up(need, 256)));
-        x->partialCap = align_up(need, 256);
-    }
     ExchangeParams X;
     memset(&X, 0, sizeof(X));
     X.world = x->world; X.rank = x->rank; X.epoch = ++x->epoch; X.nqMax = x->nqMax; X.maxGroups = x->maxGroups;
-    X.groupCounter = x->groupCounter; X.status = x->status; X.out = out_d;
+    X.groupCounter = x->groupCounter; X.acc = x->acc; X.status = x->status; X.out = out_d;
     for (int p = 0; p < x->world; p++) X.peer[p] = x->peer[p];
     X.timeoutNs = 10LL * 1000 * 1000 * 1000;
-    k_bf_top2<true><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb_local, rows, index_offset,
-                                                                (orbb200_top2 *)x->partial, X);
+    k_bf_top2<true><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb_local, rows, index_offset, nullptr, X);
     ORB_CUDA_OK(cudaGetLastError());
     return ORBB200_OK;
 }

@@ -29,7 +29,8 @@ EXPORTS = [
     "orbb200_vocabulary_transform", "orbb200_vocabulary_transform_device", "orbb200_compute_bow_batch",
     "orbb200_compute_bow_batch_device", "orbb200_distinctive_descriptors", "orbb200_distinctive_descriptors_device",
     "orbb200_exchange_create", "orbb200_exchange_connect", "orbb200_exchange_destroy", "orbb200_match_sharded_top2_device",
-    "orbb200_exchange_status",
+    "orbb200_exchange_status", "orbb200_extract_color", "orbb200_extract_color_batch", "orbb200_cvt_gray",
+    "orbb200_undistort_keypoints", "orbb200_undistort_keypoints_device",
 ]
 
 _lib = None
@@ -79,6 +80,11 @@ def lib():
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
     L.orbb200_distinctive_descriptors.argtypes = [vp, vp, ip, vp, vp, ip]
+    L.orbb200_extract_color.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp, ip, vp]
+    L.orbb200_extract_color_batch.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp, vp, ip, vp]
+    L.orbb200_cvt_gray.argtypes = [vp, ip, ip, ip, ip, ip, vp, ip, ip]
+    L.orbb200_undistort_keypoints.argtypes = [vp, ip, vp, vp, vp, ip]
+    L.orbb200_undistort_keypoints_device.argtypes = [vp, ip, vp, vp, vp, vp]
     L.orbb200_exchange_create.argtypes = [vp, ip, ip, ip, ip, vp]
     L.orbb200_exchange_connect.argtypes = [vp, vp]
     L.orbb200_exchange_destroy.argtypes = [vp]
@@ -179,6 +185,32 @@ class ORBextractor:
         n = C.c_int(0)
         check(self.L.orbb200_extract(self.h, _p(image), w, h, image.strides[0], _p(kps), _p(desc), self.cap, C.byref(n)))
         return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_color(self, image, r_first):
+        """Tracking::GrabImage* prologue + operator(): image [H, W, 3|4] uint8, r_first = mbRGB.  The gray conversion runs
+        on the device inside the level-0 staging; mImGray is pyramid_level(0)."""
+        assert image.dtype == np.uint8 and image.ndim == 3 and image.shape[2] in (3, 4)
+        if image.strides[2] != 1 or image.strides[1] != image.shape[2]:
+            image = np.ascontiguousarray(image)
+        h, w, ch = image.shape
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int(0)
+        check(self.L.orbb200_extract_color(self.h, _p(image), w, h, image.strides[0], ch, int(bool(r_first)), _p(kps), _p(desc),
+                                           self.cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_color_batch(self, images, r_first):
+        """images: [B, H, W, 3|4] uint8 (host).  Returns (kps[B,cap], desc[B,cap,32], n[B])."""
+        B, h, w, ch = images.shape
+        assert images.dtype == np.uint8 and images.strides[3] == 1 and images.strides[2] == ch
+        ptrs = (C.c_void_p * B)(*[images.ctypes.data + b * images.strides[0] for b in range(B)])
+        kps = np.zeros((B, self.cap), KP_DTYPE)
+        desc = np.zeros((B, self.cap, 32), np.uint8)
+        n_out = np.zeros(B, np.int32)
+        check(self.L.orbb200_extract_color_batch(self.h, ptrs, B, w, h, images.strides[1], ch, int(bool(r_first)), _p(kps), _p(desc),
+                                                 self.cap, _p(n_out)))
+        return kps, desc, n_out
 
     def extract_batch(self, images, kps=None, desc=None, n_out=None):
         """images: [B,H,W] uint8 (host).  Returns (kps[B,cap], desc[B,cap,32], n[B])."""
@@ -477,6 +509,27 @@ def stereo_match(left, right, bf, b):
 
 
 # ---- multi-GPU host logic: frames and database rows are sharded per rank --------------------------
+def cvt_gray(image, r_first, device=-1):
+    """cv::cvtColor(im, gray, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) (reference Tracking.cc:177-202)"""
+    assert image.dtype == np.uint8 and image.ndim == 3 and image.shape[2] in (3, 4)
+    image = np.ascontiguousarray(image)
+    h, w, ch = image.shape
+    gray = np.zeros((h, w), np.uint8)
+    check(lib().orbb200_cvt_gray(_p(image), w, h, image.strides[0], ch, int(bool(r_first)), _p(gray), w, device))
+    return gray
+
+
+def undistort_keypoints(kps, cam, dist_coef, device=-1):
+    """Frame::UndistortKeyPoints (reference Frame.cc:470-515): kps [N] KP_DTYPE -> copy with undistorted x, y"""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    out = np.zeros(len(kps), KP_DTYPE)
+    cam = np.ascontiguousarray(cam, np.float32)
+    dc = np.ascontiguousarray(dist_coef, np.float32)
+    assert cam.size == 4 and dc.size == 5
+    check(lib().orbb200_undistort_keypoints(_p(kps), len(kps), _p(cam), _p(dc), _p(out), device))
+    return out
+
+
 class ShardedMatcher:
     """Config 5 on N GPUs (one process per GPU): brute-force top-2 over a row-sharded database with the exchange step
     fused into the search kernel (peer stores over NVLink + flags, include/orbb200.h "config 5 on N GPUs").

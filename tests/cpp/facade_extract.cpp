@@ -27,8 +27,38 @@ static void dump(const std::string &path, const void *p, size_t bytes)
     fclose(f);
 }
 
+// Tracking::GrabImageMonocular on a colour frame (src/Tracking.cc:255-266) + Frame::UndistortKeyPoints (src/Frame.cc:470-515):
+//   facade_extract --color <w> <h> <channels> <bRGB> <color.raw> <out_prefix> <fx> <fy> <cx> <cy> <k1> <k2> <p1> <p2> <k3>
+static int color_main(int argc, char **argv)
+{
+    if (argc < 17) return 2;
+    const int w = atoi(argv[2]), h = atoi(argv[3]), ch = atoi(argv[4]);
+    const bool bRGB = atoi(argv[5]) != 0;
+    const std::string out = argv[7];
+    cv::Mat im(h, w, ch == 3 ? CV_8UC3 : CV_8UC4);
+    FILE *f = fopen(argv[6], "rb");
+    if (!f || fread(im.data, 1, (size_t)w * h * ch, f) != (size_t)w * h * ch) return 3;
+    fclose(f);
+    ORBextractor *mpIniORBextractor = new ORBextractor(2000, 1.2f, 8, 20, 7); // Tracking.cc:130: 2 * nFeatures for the mono initialiser
+    std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
+    cv::Mat mDescriptors, mImGray;
+    mpIniORBextractor->ExtractColor(im, bRGB, mvKeys, mDescriptors, &mImGray);
+    cv::Mat mK = cv::Mat::zeros(3, 3, CV_32F), mDistCoef(5, 1, CV_32F);
+    mK.at<float>(0, 0) = (float)atof(argv[8]); mK.at<float>(1, 1) = (float)atof(argv[9]);
+    mK.at<float>(0, 2) = (float)atof(argv[10]); mK.at<float>(1, 2) = (float)atof(argv[11]); mK.at<float>(2, 2) = 1.f;
+    for (int i = 0; i < 5; i++) mDistCoef.at<float>(i, 0) = (float)atof(argv[12 + i]);
+    orbb200::UndistortKeyPoints(mvKeys, mK, mDistCoef, mvKeysUn);
+    dump(out + "_kps.bin", mvKeys.data(), mvKeys.size() * sizeof(cv::KeyPoint));
+    dump(out + "_kpsun.bin", mvKeysUn.data(), mvKeysUn.size() * sizeof(cv::KeyPoint));
+    dump(out + "_desc.bin", mDescriptors.data, (size_t)mDescriptors.rows * 32);
+    dump(out + "_gray.bin", mImGray.data, (size_t)w * h);
+    printf("N %zu\n", mvKeys.size());
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc > 1 && std::string(argv[1]) == "--color") return color_main(argc, argv);
     if (argc < 11) { fprintf(stderr, "usage\n"); return 2; }
     const int w = atoi(argv[1]), h = atoi(argv[2]), nfeat = atoi(argv[3]);
     const float scale = (float)atof(argv[4]);

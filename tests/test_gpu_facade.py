@@ -134,3 +134,31 @@ def test_facade_distinctive_descriptors_equals_reference_loop(seed, nkf, nmp):
     r = subprocess.run([exe, str(seed), str(nkf), str(nmp)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
     assert int(r.stdout.split()[2]) > nmp // 2
+
+
+def test_facade_color_extraction_and_undistort(tmp_path):
+    """ORBextractor::ExtractColor (cvtColor prologue fused into the extraction) + orbb200::UndistortKeyPoints driven like
+    Tracking::GrabImageMonocular / Frame::Frame on a TUM1-shaped colour frame, against the oracles."""
+    import prologue_oracle as po
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_extract.bin")
+    base = synth.textured_frame(640, 480, 4321)
+    rng = np.random.default_rng(6)
+    img = np.stack([np.clip(base.astype(np.int32) + rng.integers(-25, 26, base.shape), 0, 255).astype(np.uint8) for _ in range(3)], axis=2)
+    raw = str(tmp_path / "c.raw")
+    img.tofile(raw)
+    cam = ["517.306408", "516.469215", "318.643040", "255.313989"]
+    dist = ["0.262383", "-0.953104", "-0.005358", "0.002628", "1.163314"]
+    out = str(tmp_path / "o")
+    r = subprocess.run([exe, "--color", "640", "480", "3", "1", raw, out] + cam + dist, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr + r.stdout
+    gray = po.cvt_gray(img, 1)
+    assert np.array_equal(np.fromfile(out + "_gray.bin", np.uint8).reshape(480, 640), gray)
+    kps = np.fromfile(out + "_kps.bin", orbb200.KP_DTYPE)
+    kun = np.fromfile(out + "_kpsun.bin", orbb200.KP_DTYPE)
+    kr, dr = ref_cpu.RefExtractor(2000, 1.2, 8, 20, 7).extract(gray)
+    assert len(kps) == len(kr) >= 2000
+    for f in ("x", "y", "size", "response", "octave"):
+        assert np.array_equal(kps[f], kr[f]), f
+    und = po.undistort_points(np.stack([kps["x"], kps["y"]], axis=1), np.array(cam, np.float32), np.array(dist, np.float32))
+    assert np.array_equal(kun["x"].view(np.uint32), und[:, 0].view(np.uint32)) and np.array_equal(kun["y"].view(np.uint32), und[:, 1].view(np.uint32))
+    assert np.array_equal(kun["octave"], kps["octave"]) and np.array_equal(kun["angle"], kps["angle"])
