@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_c
     extern __shared__ __align__(16) unsigned char dsm[];
     __shared__ int scanTmp[34];
     __shared__ int sh_size, sh_finish, sh_mode, sh_seq, sh_nexp, sh_rstar;
-    const int l = blockIdx.x, b = blockIdx.y;
+    const int l = blockIdx.y, b = blockIdx.x; // level-major launch order: the heavy level-0 blocks start first, the light ones fill the tail
     const LevelGeom g = P.geom[l];
     const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = NT >> 5;
     const int C = g.nodeCap, N = g.nfeat;
