@@ -40,14 +40,15 @@ struct orbb200_extractor {
     int *d_stSad = nullptr, *d_stN = nullptr, *d_stRows = nullptr;
     size_t stElems = 0, stRowElems = 0;
     int stPairs = 0, stOutCap = 0;
-    // host-API pipeline (orbb200_extract_batch): copy / D2H streams, double-buffered packed staging
+    // host-API pipeline (orbb200_extract_batch): copy / D2H streams, multi-buffered packed staging
     // and up to PIPE_STREAMS compute streams so that the latency-bound tail of one chunk (quadtree passes) overlaps
     // the throughput-bound head of the next (all per-image workspaces are disjoint between chunks)
     static constexpr int PIPE_STREAMS = 8;
     cudaStream_t copyStream = nullptr, d2hStream = nullptr, workStream[PIPE_STREAMS] = {};
-    cudaEvent_t evH2D[2] = {nullptr, nullptr}, evDone[2] = {nullptr, nullptr}, evStaged[2] = {nullptr, nullptr};
+    static constexpr int PIPE_STAGES = 6; // staging buffers: the H2D copies run up to 6 chunks ahead of the stage kernels
+    cudaEvent_t evH2D[PIPE_STAGES] = {}, evDone[PIPE_STAGES] = {}, evStaged[PIPE_STAGES] = {};
     cudaEvent_t evWork[PIPE_STREAMS] = {}, evBegin = nullptr;
-    uint8_t *d_stage[2] = {nullptr, nullptr};
+    uint8_t *d_stage[PIPE_STAGES] = {};
     size_t stageBytes = 0;
     int pipeChunk = 16, pipeStreams = 8, devChunk = 0;
     // last call

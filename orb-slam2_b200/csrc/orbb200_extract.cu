@@ -4,13 +4,16 @@
 #include <stdarg.h>
 
 #include <algorithm>
+#include <chrono>
 #include <new>
+#include <stdlib.h>
 
 #define ORBB200_EXTRACT_IMPL
 #include "blur_kernel.cuh"
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
 #include "fast_kernel.cuh"
+#include "fast2_kernel.cuh"
 #include "stage_kernel.cuh"
 #include "octree_kernel.cuh"
 
@@ -213,7 +216,7 @@ int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes)
 {
     if (!e->copyStream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
     if (!e->d2hStream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&e->d2hStream, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < orbb200_extractor::PIPE_STAGES; i++) {
         if (!e->evH2D[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evH2D[i], cudaEventDisableTiming));
         if (!e->evDone[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evDone[i], cudaEventDisableTiming));
         if (!e->evStaged[i]) ORB_CUDA_OK(cudaEventCreateWithFlags(&e->evStaged[i], cudaEventDisableTiming));
@@ -227,7 +230,7 @@ int extractor_ensure_pipeline(orbb200_extractor *e, size_t stageBytes)
         ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
         ORB_CUDA_OK(cudaStreamSynchronize(e->copyStream));
         for (int i = 0; i < orbb200_extractor::PIPE_STREAMS; i++) ORB_CUDA_OK(cudaStreamSynchronize(e->workStream[i]));
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < orbb200_extractor::PIPE_STAGES; i++) {
             if (e->d_stage[i]) { cudaFree(e->d_stage[i]); e->d_stage[i] = nullptr; }
             ORB_CUDA_OK(cudaMalloc((void **)&e->d_stage[i], stageBytes + 256));
         }
