@@ -274,10 +274,11 @@ class ORBextractor:
 
     def stage_ms_sum(self):
         """(dict of summed stage ms, number of calls covered) since set_profiling(True)."""
-        ms = np.zeros(5, np.float32)
+        ms = np.zeros(6, np.float32)
         n = C.c_int()
-        check(self.L.orbb200_extractor_stage_ms_sum(self.h, _p(ms), 5, C.byref(n)))
-        return dict(zip(self.STAGES, ms.tolist())), n.value
+        check(self.L.orbb200_extractor_stage_ms_sum(self.h, _p(ms), 6, C.byref(n)))
+        self.extract_total_ms_sum = float(ms[5])  # first launch to last; the stages may overlap (blur on a side stream)
+        return dict(zip(self.STAGES, ms[:5].tolist())), n.value
 
     def last_launches(self):
         return self.L.orbb200_extractor_last_launches(self.h)
