@@ -282,13 +282,15 @@ def run_b200(args, rank, world, local_rank):
         dom_bytes = 0
         dom_bytes_note = "quadtree selection moves no image bytes; it is latency/serial bound (see DESIGN.md)"
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
-    # dram__bytes_read.sum + dram__bytes_write.sum of one k_fast_cells launch over 320 KITTI images, from the committed
-    # `ncu --set full` capture (profiles/r1_fast_cells_full_details_final.txt); only quoted for that kernel and batch
-    traffic = 416073984 + 61459200 if (dom == "fast_cells" and B == 320) else None
+    # dram__bytes_read.sum + dram__bytes_write.sum of one k_fast_cells2 launch over 320 KITTI images, from the committed
+    # `ncu --set full` capture (profiles/r1_fast_cells2_full_details.txt); only quoted for that kernel and batch
+    traffic = 416182272 + 60045312 if (dom == "fast_cells" and B == 320) else None
+    kernel_names = {"pyramid": "k_pyramid_resize", "fast_cells": "k_fast_cells2", "octree_select": "k_octree_select",
+                    "blur7": "k_blur7", "orient_describe": "k_orient_describe"}
     roofline = {
-        "kernel": "k_" + dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "kernel": kernel_names.get(dom, "k_" + dom), "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
         "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-        "bound_note": "reported against HBM as the contract asks; ncu shows the kernel ALU-pipe bound (78 % ALU, 2.5 % DRAM)",
+        "bound_note": "reported against HBM as the contract asks; ncu shows the kernel issue / ALU-pipe bound (73 % issue slots, 66 % ALU, 3 % DRAM)",
         "launches_per_step": dom_launches, "ms_per_step": stage_ms[dom], "algorithmic_bytes_per_step": dom_bytes,
         "stage_ms_per_step": stage_ms,
         "path": {"algorithmic_bytes_per_image": abytes_img, "achieved": value / world * abytes_img / 1e9,

@@ -104,8 +104,8 @@ __global__ void __launch_bounds__(FC_THREADS, 6) k_fast_cells2(const __grid_cons
     const int ppr = (iw + 1) >> 1;
     const int lprShift = ppr <= 8 ? 3 : (ppr <= 16 ? 4 : 5);
     const int lpr = 1 << lprShift, rpw = 32 >> lprShift;
-    const int ngroups = (ih + rpw - 1) / rpw;
-    const int gpw = (ngroups + FC_WARPS - 1) / FC_WARPS;
+    const int ngroups = (int)((unsigned int)(ih + rpw - 1) >> (5 - lprShift)); // / rpw
+    const int gpw = (int)((unsigned int)(ngroups + FC_WARPS - 1) / (unsigned int)FC_WARPS);
     const int g0 = wid * gpw, g1 = min(g0 + gpw, ngroups);
     const int xl = lane & (lpr - 1), yl = lane >> lprShift;
     const int x = 2 * xl;
