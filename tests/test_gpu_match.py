@@ -212,3 +212,31 @@ def test_distinctive_descriptors_keyframe_sized_batch():
     ri, rm = ref_cpu.distinctive_descriptors(desc, offs)
     assert np.array_equal(gi, ri) and np.array_equal(gm, rm)
     assert (gi >= 0).all() and (gi < np.diff(offs)).all()
+
+
+def test_bruteforce_full_config5_size_properties():
+    """BASELINE config 5 at its full size (2048 queries x 1 048 576 rows): size-independent properties -- every planted
+    near-duplicate (<= 60 flipped bits; random rows sit near 128 +- 8) is the best match at its planted position, best <=
+    second, the flat search equals the fold of 8 row shards searched separately (the N-GPU structure), and a sample of
+    queries equals the CPU oracle over the whole database."""
+    nq, ndb = 2048, 1 << 20
+    q, db, pos = synth.descriptor_db(nq, ndb, seed=7)
+    m = orbb200.ORBmatcher()
+    t = m.bruteforce_top2(q, db)
+    assert np.array_equal(t["best_idx"], pos.astype(np.int32))
+    assert (t["best_dist"] <= 60).all() and (t["best_dist"] <= t["second_dist"]).all() and (t["second_dist"] > 60).all()
+    assert (t["second_idx"] != t["best_idx"]).all() and (t["second_idx"] >= 0).all()
+    d_best = np.unpackbits(q ^ db[t["best_idx"]], axis=1).sum(axis=1)
+    d_second = np.unpackbits(q ^ db[t["second_idx"]], axis=1).sum(axis=1)
+    assert np.array_equal(d_best, t["best_dist"]) and np.array_equal(d_second, t["second_dist"])
+    shards = 8
+    per = ndb // shards
+    parts = np.zeros((shards, nq), orbb200.TOP2_DTYPE)
+    for s in range(shards):
+        p = m.bruteforce_top2(q, db[s * per:(s + 1) * per])
+        for f in ("best_idx", "second_idx"):
+            p[f] = np.where(p[f] >= 0, p[f] + s * per, -1)
+        parts[s] = p
+    _eq(m.merge_top2(parts), t)
+    sample = np.arange(0, nq, 128)
+    _eq(t[sample], ref_cpu.bf_top2(q[sample], db, use_popcnt=True))
