@@ -187,6 +187,18 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
                           float invH, int cols, int rows, const float *windows, const uint8_t *qdesc, int nq,
                           int *cand_offsets, int *cand_idx, uint16_t *dist, int cand_cap, int device);
 
+/* The same with everything resident in HBM and asynchronous on `stream` (the windowed searches chained
+ * behind the extraction without a host round trip).  tkp_d / tdesc_d may be one image's slice of the block
+ * orbb200_extract_batch_device wrote (tkp_d = kps_d + i*cap, tdesc_d = desc_d + i*cap*32, nt = cap, nt_d = n_out_d + i:
+ * when nt_d is not NULL the keypoint count is read on the device, clipped to nt).  workspace_d: cols*rows + 1 + nt ints.
+ * cand_offsets_d[nq + 1] receives the CSR offsets (cand_offsets_d[nq] = total number of candidates); candidates beyond
+ * cand_cap are not written -- the caller compares the total with cand_cap after reading the offsets.  Same order and
+ * same distances as orbb200_window_search. */
+int orbb200_window_search_device(const orbb200_keypoint *tkp_d, const uint8_t *tdesc_d, int nt, const int *nt_d, float minX,
+                                 float minY, float invW, float invH, int cols, int rows, const float *windows_d,
+                                 const uint8_t *qdesc_d, int nq, int *cand_offsets_d, int *cand_idx_d, uint16_t *dist_d,
+                                 int cand_cap, int *workspace_d, void *stream);
+
 /* merge of per-shard top-2 results (config 5, database sharded by rows; shard s's indices already global):
  * parts[s*nq + i]; ties on best_dist go to the lowest shard (= lowest global index, first-seen rule). */
 int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);

@@ -252,6 +252,35 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
     return ORBB200_OK;
 }
 
+int orbb200_window_search_device(const orbb200_keypoint *tkp_d, const uint8_t *tdesc_d, int nt, const int *nt_d, float minX, float minY,
+                                 float invW, float invH, int cols, int rows, const float *windows_d, const uint8_t *qdesc_d, int nq,
+                                 int *cand_offsets_d, int *cand_idx_d, uint16_t *dist_d, int cand_cap, int *workspace_d, void *stream)
+{
+    ORB_ARG_OK(cand_offsets_d != nullptr && stream != nullptr, "cand_offsets_d / stream is null");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nq <= 0 || nt <= 0) {
+        ORB_CUDA_OK(cudaMemsetAsync(cand_offsets_d, 0, sizeof(int) * (size_t)(std::max(nq, 0) + 1), st));
+        return ORBB200_OK;
+    }
+    ORB_ARG_OK(tkp_d && tdesc_d && windows_d && qdesc_d && workspace_d && cols > 0 && rows > 0 && cols * rows <= 11000, "bad arguments");
+    ORB_ARG_OK(cand_cap >= 0 && (cand_cap == 0 || (cand_idx_d && dist_d)), "null candidate outputs");
+    ORB_ARG_OK((((size_t)tdesc_d | (size_t)qdesc_d) & 15) == 0, "descriptor arrays must be 16-byte aligned");
+    const int nc = cols * rows;
+    WindowParams W;
+    memset(&W, 0, sizeof(W));
+    W.G.kp = tkp_d; W.G.n = nt; W.G.nPtr = nt_d;
+    W.G.minX = minX; W.G.minY = minY; W.G.invW = invW; W.G.invH = invH; W.G.cols = cols; W.G.rows = rows;
+    W.G.cellStart = workspace_d; W.G.cellItems = workspace_d + nc + 1;
+    W.win = windows_d; W.qdesc = qdesc_d; W.tdesc = tdesc_d; W.nq = nq;
+    W.counts = cand_offsets_d; W.candIdx = cand_idx_d; W.dist = dist_d; W.cap = cand_cap;
+    k_grid_build<<<1, 256, (size_t)(nc + 1) * 4, st>>>(W.G);
+    k_window_count<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
+    k_scan_counts<<<1, 1024, 0, st>>>(cand_offsets_d, nq);
+    if (cand_cap > 0) k_window_fill<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
+}
+
 int orbb200_merge_top2_device(const orbb200_top2 *parts_d, int nshards, int nq, orbb200_top2 *out_d, void *stream)
 {
     ORB_ARG_OK(parts_d && out_d && nshards > 0 && nq > 0, "bad arguments");

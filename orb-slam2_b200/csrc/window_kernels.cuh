@@ -13,6 +13,7 @@ namespace orbb200 {
 struct GridParams {
     const orbb200_keypoint *kp; // target keypoints (the caller's mvKeysUn)
     int n;
+    const int *nPtr;              // when not null: the keypoint count lives on the device (min(*nPtr, n) is used)
     float minX, minY, invW, invH; // mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv
     int cols, rows;               // FRAME_GRID_COLS, FRAME_GRID_ROWS
     int *cellStart;               // [cols*rows + 1]
@@ -25,6 +26,7 @@ __global__ void __launch_bounds__(256) k_grid_build(const GridParams G)
     extern __shared__ int gsm[];
     __shared__ int scanTmp[34];
     const int nc = G.cols * G.rows, tid = threadIdx.x, NT = blockDim.x;
+    const int n = G.nPtr ? min(max(*G.nPtr, 0), G.n) : G.n;
     for (int c = tid; c <= nc; c += NT) gsm[c] = 0;
     __syncthreads();
     auto cell_of = [&](int i) {
@@ -33,7 +35,7 @@ __global__ void __launch_bounds__(256) k_grid_build(const GridParams G)
         const int py = (int)roundf(__fmul_rn(__fsub_rn(k.y, G.minY), G.invH));
         return (px < 0 || px >= G.cols || py < 0 || py >= G.rows) ? -1 : px * G.rows + py;
     };
-    for (int i = tid; i < G.n; i += NT) {
+    for (int i = tid; i < n; i += NT) {
         const int c = cell_of(i);
         if (c >= 0) atomicAdd(&gsm[c], 1);
     }
@@ -52,9 +54,9 @@ __global__ void __launch_bounds__(256) k_grid_build(const GridParams G)
     // stable fill by ONE warp walking the keypoints in index order
     if (tid < 32) {
         const unsigned int lt = (1u << tid) - 1u;
-        for (int base = 0; base < G.n; base += 32) {
+        for (int base = 0; base < n; base += 32) {
             const int i = base + tid;
-            const int c = i < G.n ? cell_of(i) : -1;
+            const int c = i < n ? cell_of(i) : -1;
             const unsigned int act = __ballot_sync(0xffffffffu, c >= 0);
             if (c >= 0) {
                 const unsigned int peers = __match_any_sync(act, c);

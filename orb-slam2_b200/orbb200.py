@@ -30,7 +30,7 @@ EXPORTS = [
     "orbb200_compute_bow_batch_device", "orbb200_distinctive_descriptors", "orbb200_distinctive_descriptors_device",
     "orbb200_exchange_create", "orbb200_exchange_connect", "orbb200_exchange_destroy", "orbb200_match_sharded_top2_device",
     "orbb200_exchange_status", "orbb200_extract_color", "orbb200_extract_color_batch", "orbb200_cvt_gray",
-    "orbb200_undistort_keypoints", "orbb200_undistort_keypoints_device",
+    "orbb200_undistort_keypoints", "orbb200_undistort_keypoints_device", "orbb200_window_search_device",
 ]
 
 _lib = None
@@ -85,6 +85,7 @@ def lib():
     L.orbb200_cvt_gray.argtypes = [vp, ip, ip, ip, ip, ip, vp, ip, ip]
     L.orbb200_undistort_keypoints.argtypes = [vp, ip, vp, vp, vp, ip]
     L.orbb200_undistort_keypoints_device.argtypes = [vp, ip, vp, vp, vp, vp]
+    L.orbb200_window_search_device.argtypes = [vp, vp, ip, vp, fp, fp, fp, fp, ip, ip, vp, vp, ip, vp, vp, vp, ip, vp, vp]
     L.orbb200_exchange_create.argtypes = [vp, ip, ip, ip, ip, vp]
     L.orbb200_exchange_connect.argtypes = [vp, vp]
     L.orbb200_exchange_destroy.argtypes = [vp]

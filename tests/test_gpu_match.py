@@ -240,3 +240,60 @@ def test_bruteforce_full_config5_size_properties():
     _eq(m.merge_top2(parts), t)
     sample = np.arange(0, nq, 128)
     _eq(t[sample], ref_cpu.bf_top2(q[sample], db, use_popcnt=True))
+
+
+def test_window_search_device_chained_behind_extraction(configs):
+    """the windowed search on the device-resident outputs of orbb200_extract_batch_device (keypoint count
+    read on the device, no host round trip) == orbb200_window_search on the downloaded outputs; a too small cand_cap only
+    drops the tail and still reports the total."""
+    import ctypes as C
+    import torch
+    w, h, nf, sfac, nl, ini, mn = configs["tum"]
+    imgs = np.stack([synth.textured_frame(w, h, 900 + i) for i in range(2)])
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    cap = ex.cap
+    dev = torch.device("cuda", 0)
+    d_img = torch.from_numpy(imgs).to(dev)
+    d_kps = torch.zeros((2, cap, 7), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((2, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(2, dtype=torch.int32, device=dev)
+    ex.extract_batch_device(d_img.data_ptr(), 2, w, h, w, w * h, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+    st = ex.stream()
+    # windows around the keypoints of image 0, searched in image 1 (frame-to-frame tracking shape)
+    ex.sync()
+    n = d_n.cpu().numpy()
+    k0 = d_kps[0, :n[0]].cpu().numpy().view(orbb200.KP_DTYPE).reshape(-1)
+    k1 = d_kps[1, :n[1]].cpu().numpy().view(orbb200.KP_DTYPE).reshape(-1)
+    q0 = d_desc[0, :n[0]].cpu().numpy()
+    t1 = d_desc[1, :n[1]].cpu().numpy()
+    nq = int(n[0])
+    win = np.zeros((nq, 5), np.float32)
+    win[:, 0], win[:, 1] = k0["x"], k0["y"]
+    win[:, 2] = 15.0 * np.float32(1.2) ** k0["octave"]
+    win[:, 3] = k0["octave"] - 1
+    win[:, 4] = k0["octave"] + 1
+    cols, rows = 64, 48
+    invW, invH = float(np.float32(cols) / np.float32(w)), float(np.float32(rows) / np.float32(h))
+    offs, idx, dist = orbb200.ORBmatcher().window_search(k1, t1, (0.0, 0.0, invW, invH, cols, rows), win, q0, cap=100)
+    total = int(offs[-1])
+    assert total > 1000
+    L = orbb200.lib()
+    d_win = torch.from_numpy(win).to(dev)
+    d_ws = torch.zeros(cols * rows + 1 + cap, dtype=torch.int32, device=dev)
+    vp = C.c_void_p
+    for ccap in (total + 7, total // 2):
+        d_offs = torch.full((nq + 1,), -1, dtype=torch.int32, device=dev)
+        d_idx = torch.full((max(ccap, 1),), -1, dtype=torch.int32, device=dev)
+        d_dist = torch.zeros(max(ccap, 1), dtype=torch.int16, device=dev)
+        torch.cuda.synchronize()
+        orbb200.check(L.orbb200_window_search_device(vp(d_kps[1].data_ptr()), vp(d_desc[1].data_ptr()), cap, vp(d_n[1:].data_ptr()),
+                                                     0.0, 0.0, invW, invH, cols, rows, vp(d_win.data_ptr()), vp(d_desc[0].data_ptr()), nq,
+                                                     vp(d_offs.data_ptr()), vp(d_idx.data_ptr()), vp(d_dist.data_ptr()), ccap,
+                                                     vp(d_ws.data_ptr()), vp(st)))
+        ex.sync()
+        assert np.array_equal(d_offs.cpu().numpy(), offs)
+        m = min(ccap, total)
+        assert np.array_equal(d_idx.cpu().numpy()[:m], idx[:m])
+        assert np.array_equal(d_dist.cpu().numpy().view(np.uint16)[:m], dist[:m])
+        if ccap > total:
+            assert (d_idx.cpu().numpy()[total:] == -1).all()

@@ -1,5 +1,7 @@
-"""Small workload over every kernel family for compute-sanitizer runs (memcheck / racecheck / initcheck):
-   compute-sanitizer --tool memcheck python tools/sanitize_probe.py"""
+"""Small workload over every kernel family (extraction on four shapes, colour input, stereo, brute force, distinctive
+descriptors, undistortion): the input of a compute-sanitizer run where the pool allows one
+(compute-sanitizer --tool memcheck python tools/sanitize_probe.py -- closed on this round's pool), and a quick
+all-kernels smoke otherwise."""
 import os
 import sys
 
