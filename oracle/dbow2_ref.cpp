@@ -10,24 +10,7 @@
 #include "DBoW2/FORB.h"
 #include "DBoW2/TemplatedVocabulary.h"
 
-// yml persistence is outside the path: the stand-in's cv::FileStorage only has to link; reaching it is a bug
-namespace cv {
-static void no_yml() { std::cerr << "dbow2_ref: cv::FileStorage is not available in the oracle build" << std::endl; abort(); }
-size_t FileNode::size() const { no_yml(); return 0; }
-FileNode FileNode::operator[](const char *) const { no_yml(); return FileNode(); }
-FileNode FileNode::operator[](const std::string &) const { no_yml(); return FileNode(); }
-FileNode FileNode::operator[](int) const { no_yml(); return FileNode(); }
-FileNode::operator int() const { no_yml(); return 0; }
-FileNode::operator double() const { no_yml(); return 0; }
-FileNode::operator std::string() const { no_yml(); return std::string(); }
-FileStorage::FileStorage(const char *, int) { no_yml(); }
-FileStorage::FileStorage(const std::string &, int) { no_yml(); }
-bool FileStorage::isOpened() const { no_yml(); return false; }
-void FileStorage::release() { no_yml(); }
-FileNode FileStorage::operator[](const std::string &) const { no_yml(); return FileNode(); }
-FileNode FileStorage::operator[](const char *) const { no_yml(); return FileNode(); }
-template <typename T> FileStorage &operator<<(FileStorage &fs, const T &) { no_yml(); return fs; }
-} // namespace cv
+// yml persistence is outside the path: cv::FileStorage is an aborting stub in oracle/cv_shim_impl.cpp
 
 namespace {
 typedef DBoW2::TemplatedVocabulary<DBoW2::FORB::TDescriptor, DBoW2::FORB> Voc; // include/ORBVocabulary.h:31-32
