@@ -58,9 +58,18 @@ int orbb200_level_tables(const orbb200_extractor *e, float *scale, float *inv_sc
 int orbb200_compute_level_tables(int nfeatures, float scaleFactor, int nlevels, float *scale, float *inv_scale,
                                  float *sigma2, float *inv_sigma2, int *nfeat, int *umax);
 
-/* upper bound on keypoints per image for this handle (DistributeOctTree can exceed the per-level quota by
- * up to 3 nodes: src/ORBextractor.cc:879).  Use it to size kps/desc. */
+/* keypoints per image when every level stays within its quota: sum of nfeat[l] + 3 (DistributeOctTree can exceed the quota by
+ * up to 3 nodes: src/ORBextractor.cc:879).  NOT a bound for wide images with a small quota -- see the shape-aware call below. */
 int orbb200_max_keypoints(const orbb200_extractor *e);
+
+/* upper bound on keypoints per image of this shape: per level max(nfeat[l] + 3, 4 * nIni_l), nIni_l = round(width / height) of
+ * the level's bordered area -- the first DistributeOctTree pass splits all nIni roots whatever the quota is
+ * (src/ORBextractor.cc:624-760) and the reference never truncates.  Use it to size kps / desc. */
+int orbb200_max_keypoints_for_shape(const orbb200_extractor *e, int width, int height);
+
+/* the `cap` of the last extraction on this handle (0 before the first): the row length of its device-resident outputs and the
+ * number of floats orbb200_stereo_match may write per side */
+int orbb200_last_capacity(const orbb200_extractor *e);
 
 /* replaces ORBextractor::operator()(image, mask, keypoints, descriptors) (include/ORBextractor.h:74-76,
  * src/ORBextractor.cc:1261-1339) for one 8-bit single-channel image.  kps[cap], desc[cap*32] are host

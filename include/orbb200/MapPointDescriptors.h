@@ -29,7 +29,12 @@
 #endif
 #include "../orbb200.h"
 
-namespace ORB_SLAM2 {
+/* The classes live in ORB_SLAM2 so that the reference's callers compile unchanged.  A test that links the reference's own
+   classes of the same name beside these (tests/cpp/ref_match.cpp) renames the namespace with -DORBB200_NAMESPACE=... */
+#ifndef ORBB200_NAMESPACE
+#define ORBB200_NAMESPACE ORB_SLAM2
+#endif
+namespace ORBB200_NAMESPACE {
 
 // groups[g] = vDescriptors of map point g (:270-299), each a 1x32 CV_8U row.  best[g] = BestIdx of :319-337, or -1 when the
 // group is empty (the reference returns before touching mDescriptor, :281,296).  Returns false on a device error (best is
@@ -68,6 +73,6 @@ template <class MapPointT> void ComputeDistinctiveDescriptorsBatch(const std::ve
         if (points[g] && best[g] >= 0) points[g]->SetDescriptor(groups[g][best[g]].clone());
 }
 
-} // namespace ORB_SLAM2
+} // namespace ORBB200_NAMESPACE (ORB_SLAM2 by default)
 
 #endif

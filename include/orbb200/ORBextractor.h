@@ -35,7 +35,12 @@
 #endif
 #include "../orbb200.h"
 
-namespace ORB_SLAM2 {
+/* The classes live in ORB_SLAM2 so that the reference's callers compile unchanged.  A test that links the reference's own
+   classes of the same name beside these (tests/cpp/ref_match.cpp) renames the namespace with -DORBB200_NAMESPACE=... */
+#ifndef ORBB200_NAMESPACE
+#define ORBB200_NAMESPACE ORB_SLAM2
+#endif
+namespace ORBB200_NAMESPACE {
 
 class ORBextractor {
 public:
@@ -73,7 +78,7 @@ public:
         _keypoints.clear();
         if (image.type() != CV_8UC1) { fail("image must be CV_8UC1", _descriptors); return; }
         if (!ensure_handle()) { fail(orbb200_last_error(), _descriptors); return; }
-        const int cap = orbb200_max_keypoints(handle_);
+        const int cap = orbb200_max_keypoints_for_shape(handle_, image.cols, image.rows);
         _keypoints.resize(cap);
         descBuf_.resize((size_t)cap * 32);
         int n = 0;
@@ -102,7 +107,7 @@ public:
         const int ch = imColor.channels();
         if (imColor.depth() != CV_8U || (ch != 3 && ch != 4)) { fail("colour image must be CV_8UC3 or CV_8UC4", _descriptors); return; }
         if (!ensure_handle()) { fail(orbb200_last_error(), _descriptors); return; }
-        const int cap = orbb200_max_keypoints(handle_);
+        const int cap = orbb200_max_keypoints_for_shape(handle_, imColor.cols, imColor.rows);
         _keypoints.resize(cap);
         descBuf_.resize((size_t)cap * 32);
         int n = 0;
@@ -179,7 +184,7 @@ protected:
     std::vector<unsigned char> descBuf_;
 };
 
-} // namespace ORB_SLAM2
+} // namespace ORBB200_NAMESPACE (ORB_SLAM2 by default)
 
 namespace orbb200 {
 
@@ -187,10 +192,10 @@ namespace orbb200 {
  * outputs of the last operator() call of both extractors.  mvuRight / mvDepth get N = #left keypoints entries
  * (-1 where unmatched), exactly what the reference leaves in Frame::mvuRight / mvDepth.  Returns the match count
  * (or -1 on error, after printing it). */
-inline int ComputeStereoMatches(ORB_SLAM2::ORBextractor &left, ORB_SLAM2::ORBextractor &right, int nLeft, float mbf, float mb,
+inline int ComputeStereoMatches(ORBB200_NAMESPACE::ORBextractor &left, ORBB200_NAMESPACE::ORBextractor &right, int nLeft, float mbf, float mb,
                                 std::vector<float> &mvuRight, std::vector<float> &mvDepth)
 {
-    const int cap = orbb200_max_keypoints(left.Handle());
+    const int cap = orbb200_last_capacity(left.Handle());
     std::vector<float> u(cap > 0 ? cap : 1, -1.f), d(cap > 0 ? cap : 1, -1.f);
     int nvalid = 0;
     mvuRight.assign(nLeft, -1.0f);

@@ -15,8 +15,9 @@
  * and this repo's tests bind them to small stand-ins (tests/cpp/facade_match.cpp).  The windowed searches send
  * their windows to orbb200_window_search (grid build + GetFeaturesInArea + distances on the device); the BoW-node
  * searches send CSR lists to orbb200_candidate_distances.  All twelve public searches of the reference class are here
- * (M1-M9 of SURVEY.md 8a plus the Sim3 overloads of loop closing); pose arithmetic on the host follows cv::gemm /
- * cv::norm / Mat::dot for CV_32F (double accumulation, one narrowing) so projections agree to the bit.
+ * (M1-M9 of SURVEY.md 8a plus the Sim3 overloads of loop closing); pose arithmetic on the host follows OpenCV's evaluation
+ * of the reference's CV_32F expressions (MatExpr folding, cv::gemm's float small-matrix branch vs its double general branch,
+ * cv::norm / Mat::dot in double) so projections agree to the bit; tests/cpp/ref_match.cpp checks it against the compiled reference.
  */
 #ifndef ORBB200_ORBMATCHER_H
 #define ORBB200_ORBMATCHER_H
@@ -37,7 +38,19 @@
 #endif
 #include "../orbb200.h"
 
-namespace ORB_SLAM2 {
+/* The classes live in ORB_SLAM2 so that the reference's callers compile unchanged.  A test that links the reference's own
+   classes of the same name beside these (tests/cpp/ref_match.cpp) renames the namespace with -DORBB200_NAMESPACE=... */
+#ifndef ORBB200_NAMESPACE
+#define ORBB200_NAMESPACE ORB_SLAM2
+#endif
+/* the restated OpenCV float accumulations must not be contracted into FMAs even when the including project builds with
+   -O3 -march=native (the reference's CMake flags) */
+#if defined(__GNUC__) && !defined(__clang__)
+#define ORBB200_NO_FMA __attribute__((optimize("-ffp-contract=off")))
+#else
+#define ORBB200_NO_FMA
+#endif
+namespace ORBB200_NAMESPACE {
 
 class ORBmatcher {
 public:
@@ -200,9 +213,9 @@ public:
         float Rcw[9], tcw[3], Rlw[9], tlw[3];
         pose_Rt(CurrentFrame.mTcw, Rcw, tcw);
         pose_Rt(LastFrame.mTcw, Rlw, tlw);
-        // twc = -Rcw^T * tcw ; tlc = Rlw * twc + tlw  (cv::gemm accumulates 32F products in double)
+        // twc = -Rcw^T * tcw (transposed operand: double accumulation) ; tlc = Rlw * twc + tlw (small-matrix branch: float)
         float twc[3], tlc[3];
-        for (int i = 0; i < 3; i++) twc[i] = -(float)((double)Rcw[i] * tcw[0] + (double)Rcw[3 + i] * tcw[1] + (double)Rcw[6 + i] * tcw[2]);
+        camera_centre(Rcw, tcw, twc);
         mat_Rx_t(Rlw, twc, tlw, tlc);
         const bool bForward = tlc[2] > CurrentFrame.mb && !bMono;
         const bool bBackward = -tlc[2] > CurrentFrame.mb && !bMono;
@@ -757,8 +770,7 @@ public:
                 t2w[r] = d.template at<float>(r, 0);
                 t12f[r] = t12.template at<float>(r, 0);
             }
-            for (int r = 0; r < 3; r++)
-                t21[r] = -(float)((double)sR21[3 * r] * t12f[0] + (double)sR21[3 * r + 1] * t12f[1] + (double)sR21[3 * r + 2] * t12f[2]);
+            mat_neg_Rx(sR21, t12f, t21); // t21 = -sR21*t12
         }
         const std::vector<MapPointT *> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
         const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
@@ -912,14 +924,31 @@ protected:
             t[r] = T.at<float>(r, 3);
         }
     }
-    // y = R*x + t as cv::gemm evaluates it for CV_32F operands: products and the added term accumulate in double
-    static void mat_Rx_t(const float *R, const float *x, const float *t, float *y)
+    // y = R*x + t as OpenCV evaluates `R*x + t` for CV_32F operands: the expression folds into ONE cv::gemm(R, x, 1, t, 1), and
+    // for an untransposed product with inner length 2..4 gemm takes its small-matrix branch -- the three products accumulate
+    // left to right in FLOAT, then (float)(sum*alpha + t*beta) in double (measured against cv2.gemm: tests/test_ref_pin.py).
+    ORBB200_NO_FMA static void mat_Rx_t(const float *R, const float *x, const float *t, float *y)
     {
-        for (int r = 0; r < 3; r++)
-            y[r] = (float)((double)R[3 * r] * x[0] + (double)R[3 * r + 1] * x[1] + (double)R[3 * r + 2] * x[2] + (double)t[r]);
+        for (int r = 0; r < 3; r++) {
+            float s = R[3 * r] * x[0];
+            s = s + R[3 * r + 1] * x[1];
+            s = s + R[3 * r + 2] * x[2];
+            y[r] = (float)((double)s + (double)t[r]);
+        }
+    }
+    // y = -(R*x): cv::gemm(R, x, -1, noArray(), 0) in the same small-matrix branch (float accumulation, exact negation)
+    ORBB200_NO_FMA static void mat_neg_Rx(const float *R, const float *x, float *y)
+    {
+        for (int r = 0; r < 3; r++) {
+            float s = R[3 * r] * x[0];
+            s = s + R[3 * r + 1] * x[1];
+            s = s + R[3 * r + 2] * x[2];
+            y[r] = -s;
+        }
     }
 
-    // Ow = -R^T * t (cv::gemm with alpha = -1: the double sum is negated, then narrowed)
+    // Ow = -R^T * t: a TRANSPOSED operand sends cv::gemm down its general branch (products accumulate in double in k order;
+    // alpha = -1 negates the double sum, one narrowing)
     static void camera_centre(const float *R, const float *t, float *Ow)
     {
         for (int i = 0; i < 3; i++) Ow[i] = -(float)((double)R[i] * t[0] + (double)R[3 + i] * t[1] + (double)R[6 + i] * t[2]);
@@ -1122,6 +1151,6 @@ protected:
     int device_;
 };
 
-} // namespace ORB_SLAM2
+} // namespace ORBB200_NAMESPACE (ORB_SLAM2 by default)
 
 #endif /* ORBB200_ORBMATCHER_H */

@@ -148,6 +148,19 @@ int orbb200_match_bruteforce_top2(const uint8_t *q, int nq, const uint8_t *db, i
     return ORBB200_OK;
 }
 
+/* CSR candidate lists come from the caller's feature vectors: a bad index would read outside the target matrix on the device,
+   so the lists are validated on the host (O(total), negligible beside the copy) */
+static int csr_valid(const int *offs, int nq, const int *idx, int nt)
+{
+    if (offs[0] != 0) return 0;
+    for (int i = 0; i < nq; i++)
+        if (offs[i + 1] < offs[i]) return 0;
+    const int total = offs[nq];
+    for (int c = 0; c < total; c++)
+        if ((unsigned)idx[c] >= (unsigned)nt) return 0;
+    return 1;
+}
+
 int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets, const int *cand_idx,
                              orbb200_top2 *out, int device)
 {
@@ -155,6 +168,7 @@ int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt,
     ORB_ARG_OK(q && cand_offsets && out, "null pointer");
     const int total = cand_offsets[nq];
     ORB_ARG_OK(total == 0 || (t && cand_idx && nt > 0), "candidates without targets");
+    ORB_ARG_OK(total >= 0 && (total == 0 ? cand_offsets[0] == 0 : csr_valid(cand_offsets, nq, cand_idx, nt)), "candidate lists: offsets not ascending from 0 or index outside [0, nt)");
     int rc = scratch_bind(device);
     if (rc) return rc;
     void *dq, *dt, *dout, *doffs, *didx;
@@ -182,6 +196,7 @@ int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int 
     const int total = cand_offsets[nq];
     if (total <= 0) return ORBB200_OK;
     ORB_ARG_OK(t && cand_idx && dist && nt > 0, "candidates without targets");
+    ORB_ARG_OK(csr_valid(cand_offsets, nq, cand_idx, nt), "candidate lists: offsets not ascending from 0 or index outside [0, nt)");
     int rc = scratch_bind(device);
     if (rc) return rc;
     void *dq, *dt, *dout, *doffs, *didx;

@@ -17,7 +17,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
 
 EXPORTS = [
-    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints",
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
@@ -57,6 +57,8 @@ def lib():
     L.orbb200_level_tables.argtypes = [vp, vp, vp, vp, vp, vp]
     L.orbb200_compute_level_tables.argtypes = [ip, fp, ip, vp, vp, vp, vp, vp, vp]
     L.orbb200_max_keypoints.argtypes = [vp]
+    L.orbb200_max_keypoints_for_shape.argtypes = [vp, ip, ip]
+    L.orbb200_last_capacity.argtypes = [vp]
     L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch_device.argtypes = [vp, vp, ip, ip, ip, ip, sz, vp, vp, ip, vp]
@@ -154,6 +156,11 @@ class ORBextractor:
         except Exception:
             pass
 
+    def _fit(self, w, h):
+        """grow self.cap to the bound for this image shape: max(nfeat + 3, 4 * nIni) per level (a wide image with a small quota
+        returns more keypoints than its quota, src/ORBextractor.cc:624-760)"""
+        self.cap = max(self.cap, self.L.orbb200_max_keypoints_for_shape(self.h, int(w), int(h)))
+
     # accessors (reference ORBextractor.h:78-98)
     def GetLevels(self):
         return self.nlevels
@@ -181,6 +188,7 @@ class ORBextractor:
         if image.strides[1] != 1:
             image = np.ascontiguousarray(image)
         h, w = image.shape
+        self._fit(w, h)
         kps = np.zeros(self.cap, KP_DTYPE)
         desc = np.zeros((self.cap, 32), np.uint8)
         n = C.c_int(0)
@@ -194,6 +202,7 @@ class ORBextractor:
         if image.strides[2] != 1 or image.strides[1] != image.shape[2]:
             image = np.ascontiguousarray(image)
         h, w, ch = image.shape
+        self._fit(w, h)
         kps = np.zeros(self.cap, KP_DTYPE)
         desc = np.zeros((self.cap, 32), np.uint8)
         n = C.c_int(0)
@@ -204,6 +213,7 @@ class ORBextractor:
     def extract_color_batch(self, images, r_first):
         """images: [B, H, W, 3|4] uint8 (host).  Returns (kps[B,cap], desc[B,cap,32], n[B])."""
         B, h, w, ch = images.shape
+        self._fit(w, h)
         assert images.dtype == np.uint8 and images.strides[3] == 1 and images.strides[2] == ch
         ptrs = (C.c_void_p * B)(*[images.ctypes.data + b * images.strides[0] for b in range(B)])
         kps = np.zeros((B, self.cap), KP_DTYPE)
@@ -217,19 +227,21 @@ class ORBextractor:
         """images: [B,H,W] uint8 (host).  Returns (kps[B,cap], desc[B,cap,32], n[B])."""
         images = np.ascontiguousarray(images, np.uint8) if not isinstance(images, np.ndarray) else images
         B, h, w = images.shape
+        self._fit(w, h)
         stride = images.strides[1]
         ptrs = (C.c_void_p * B)(*[images.ctypes.data + b * images.strides[0] for b in range(B)])
         if kps is None:
             kps = np.zeros((B, self.cap), KP_DTYPE)
             desc = np.zeros((B, self.cap, 32), np.uint8)
             n_out = np.zeros(B, np.int32)
-        check(self.L.orbb200_extract_batch(self.h, ptrs, B, w, h, stride, _p(kps), _p(desc), self.cap, _p(n_out)))
+        check(self.L.orbb200_extract_batch(self.h, ptrs, B, w, h, stride, _p(kps), _p(desc), kps.shape[1], _p(n_out)))
         return kps, desc, n_out
 
     def extract_stereo_batch(self, images, bf, b):
         """images: [2P,H,W] uint8 (host), pair p = (2p, 2p+1).  Extraction + ComputeStereoMatches in one pipelined call.
         Returns (kps, desc, n, uRight[P,cap], depth[P,cap], n_valid[P])."""
         B, h, w = images.shape
+        self._fit(w, h)
         ptrs = (C.c_void_p * B)(*[images.ctypes.data + i * images.strides[0] for i in range(B)])
         kps = np.zeros((B, self.cap), KP_DTYPE)
         desc = np.zeros((B, self.cap, 32), np.uint8)

@@ -136,10 +136,16 @@ static void noisy_copy(const unsigned char *src, unsigned char *dst, int flips)
     for (int f = 0; f < flips; f++) { const unsigned b = rnd() % 256; dst[b >> 3] ^= (unsigned char)(1u << (b & 7)); }
 }
 
-// ---- small pose helpers of the checks below (CV_32F gemm semantics: double accumulation, one narrowing) -----------
+// ---- small pose helpers of the checks below (CV_32F gemm semantics: float small-matrix branch, double for transposed operands) ---
+// R*x + t = ONE cv::gemm(R, x, 1, t, 1) in the small-matrix branch: FLOAT accumulation left to right (pinned to cv2 in tests/test_ref_pin.py)
 static void t_Rx_t(const float *R, const float *x, const float *t, float *y)
 {
-    for (int r = 0; r < 3; r++) y[r] = (float)((double)R[3 * r] * x[0] + (double)R[3 * r + 1] * x[1] + (double)R[3 * r + 2] * x[2] + (double)t[r]);
+    for (int r = 0; r < 3; r++) {
+        float s = R[3 * r] * x[0];
+        s = s + R[3 * r + 1] * x[1];
+        s = s + R[3 * r + 2] * x[2];
+        y[r] = (float)((double)s + (double)t[r]);
+    }
 }
 static void t_centre(const float *R, const float *t, float *O)
 {
@@ -349,15 +355,17 @@ int main()
             const float *Tc = C.mTcw.ptr<float>(), *Tl = Last.mTcw.ptr<float>();
             float twc[3], tlc[3];
             for (int i = 0; i < 3; i++) twc[i] = -(float)((double)Tc[i] * Tc[3] + (double)Tc[4 + i] * Tc[7] + (double)Tc[8 + i] * Tc[11]);
-            for (int r = 0; r < 3; r++) tlc[r] = (float)((double)Tl[4 * r] * twc[0] + (double)Tl[4 * r + 1] * twc[1] + (double)Tl[4 * r + 2] * twc[2] + (double)Tl[4 * r + 3]);
+            { float Rl[9], tl[3]; for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) Rl[3 * r + c] = Tl[4 * r + c]; tl[r] = Tl[4 * r + 3]; } t_Rx_t(Rl, twc, tl, tlc); }
             const bool bForward = tlc[2] > C.mb, bBackward = -tlc[2] > C.mb;
             for (int i = 0; i < Last.N; i++) {
                 MapPoint *pMP = Last.mvpMapPoints[i];
                 if (!pMP || Last.mvbOutlier[i]) continue;
                 const float X = pMP->pos.at<float>(0, 0), Y = pMP->pos.at<float>(1, 0), Z = pMP->pos.at<float>(2, 0);
-                const float xc = (float)((double)Tc[0] * X + (double)Tc[1] * Y + (double)Tc[2] * Z + (double)Tc[3]);
-                const float yc = (float)((double)Tc[4] * X + (double)Tc[5] * Y + (double)Tc[6] * Z + (double)Tc[7]);
-                const float zc = (float)((double)Tc[8] * X + (double)Tc[9] * Y + (double)Tc[10] * Z + (double)Tc[11]);
+                float Rc[9], tc3[3], pcam[3];
+                for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) Rc[3 * r + c] = Tc[4 * r + c]; tc3[r] = Tc[4 * r + 3]; }
+                const float pw3[3] = {X, Y, Z};
+                t_Rx_t(Rc, pw3, tc3, pcam);
+                const float xc = pcam[0], yc = pcam[1], zc = pcam[2];
                 const float invzc = 1.0 / zc;
                 if (invzc < 0) continue;
                 const float u = C.fx * xc * invzc + C.cx, v = C.fy * yc * invzc + C.cy;
@@ -991,7 +999,7 @@ int main()
         float sR12[9], sR21[9], t21[3];
         const float inv = (float)(1.0 / s12);
         for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) { sR12[3 * r + c] = R12[3 * r + c] * s12; sR21[3 * r + c] = R12[3 * c + r] * inv; }
-        for (int r = 0; r < 3; r++) t21[r] = -(float)((double)sR21[3 * r] * t12[0] + (double)sR21[3 * r + 1] * t12[1] + (double)sR21[3 * r + 2] * t12[2]);
+        for (int r = 0; r < 3; r++) { float a = sR21[3 * r] * t12[0]; a = a + sR21[3 * r + 1] * t12[1]; a = a + sR21[3 * r + 2] * t12[2]; t21[r] = -a; } // gemm(sR21, t12, -1): float branch
         std::vector<MapPoint> s1(tmp.N), s2(tmp.N);
         const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, z0[3] = {0, 0, 0};
         for (int i = 0; i < tmp.N; i++) {

@@ -92,6 +92,17 @@ def test_facade_matcher_templates_equal_reference_loops():
     assert r.returncode == 0 and r.stdout.count("ok ") == 16 and "FAIL" not in r.stdout, r.stdout + r.stderr
 
 
+def test_facade_matcher_equals_compiled_reference_on_reference_types():
+    """All twelve searches of include/orbb200/ORBmatcher.h, bound to the REFERENCE's own Frame / KeyFrame / MapPoint / Map
+    classes, against the REFERENCE's own ORBmatcher.cc (oracle/_ref/liborbslam_ref.so = the unmodified sources compiled by
+    oracle/Makefile): twin worlds from one seed, every side effect serialised and compared (tests/cpp/ref_match.cpp)."""
+    exe = os.path.join(ROOT, "orb-slam2_b200", "ref_match.bin")
+    if not os.path.exists(exe):
+        pytest.skip("ref_match.bin not built (needs /root/reference at build time; it ships prebuilt to the GPU box)")
+    r = subprocess.run([exe, "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and r.stdout.count("ok ") == 3 * 18 + 1 and "FAIL" not in r.stdout, r.stdout[-4000:] + r.stderr[-2000:]
+
+
 @pytest.mark.parametrize("name,levelsup", [("a", 4), ("a", 2), ("b", 1), ("b", 4)])
 def test_facade_vocabulary_equals_reference_golden(tmp_path, name, levelsup):
     """include/orbb200/ORBVocabulary.h driven like Frame::ComputeBoW / LoopClosing::DetectLoop, against the outputs of

@@ -69,6 +69,43 @@ def test_sharded_merge_equals_flat():
     assert np.array_equal(acc, ref_acc) and acc.any() and not acc.all()
 
 
+def test_candidate_distances_equal_oracle_and_reference():
+    """orbb200_candidate_distances (k_candidate_distances): the distance step of both SearchByBoW overloads and of
+    SearchForTriangulation (src/ORBmatcher.cc:214-244, 626-650, 780-815) on random CSR candidate lists -- empty lists, lists
+    longer than a warp, repeated targets -- against the C oracle and the reference's own DescriptorDistance."""
+    rng = np.random.default_rng(21)
+    q, t, _ = synth.descriptor_db(700, 1900, seed=5)
+    sizes = rng.choice([0, 0, 1, 2, 5, 31, 32, 33, 64, 100, 257], size=len(q))
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    idx = rng.integers(0, len(t), int(offs[-1])).astype(np.int32)
+    idx[offs[5]:offs[6]] = idx[offs[5]] if sizes[5] else idx[offs[5]:offs[6]]  # one list of a single repeated target
+    m = orbb200.ORBmatcher()
+    d = m.candidate_distances(q, t, offs, idx)
+    want = np.unpackbits(np.repeat(q, sizes, axis=0) ^ t[idx], axis=1).sum(axis=1).astype(np.uint16)
+    assert np.array_equal(d, want)
+    import orbslam_ref
+    for c in rng.integers(0, len(idx), 300):
+        qi = int(np.searchsorted(offs, c, side="right") - 1)
+        assert int(d[c]) == ref_cpu.descriptor_distance(q[qi], t[idx[c]])
+        if orbslam_ref.available():
+            assert int(d[c]) == orbslam_ref.descriptor_distance(q[qi], t[idx[c]])
+    # top-2 of the same lists
+    _eq(m.match_candidates(q, t, offs, idx), ref_cpu.match_candidates(q, t, offs, idx))
+    # all lists empty / no queries
+    z = np.zeros(len(q) + 1, np.int32)
+    assert len(m.candidate_distances(q, t, z, np.zeros(0, np.int32))) == 0
+    # malformed lists are rejected on the host, not read out of bounds on the device
+    bad = idx.copy()
+    bad[3] = len(t)
+    with pytest.raises(Exception):
+        m.candidate_distances(q, t, offs, bad)
+    bad_offs = offs.copy()
+    bad_offs[4], bad_offs[5] = bad_offs[5] + 1, bad_offs[4]
+    if bad_offs[4] > bad_offs[5]:
+        with pytest.raises(Exception):
+            m.candidate_distances(q, t, bad_offs, idx)
+
+
 def test_match_candidates_equals_oracle():
     rng = np.random.default_rng(9)
     nq, nt = 1500, 1800

@@ -1,0 +1,114 @@
+"""GPU parity tests straight against the REFERENCE's own code: oracle/_ref/liborbslam_ref.so is the unmodified
+/root/reference/src/{ORBextractor,Frame,...}.cc compiled by oracle/Makefile (it ships prebuilt to the GPU box; nothing here
+reads /root/reference).  Same tolerances as tests/test_gpu_extract.py: keypoints and their ORDER bit-exact, angles within
+1e-4 rad, descriptors bit-exact for >= 99.9 % of keypoints, stereo coordinates bit-exact."""
+import numpy as np
+import pytest
+
+import orbb200
+import orbslam_ref as R
+import synth
+from test_gpu_extract import _compare
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not R.available(), reason="oracle/_ref/liborbslam_ref.so not built")]
+
+
+@pytest.mark.parametrize("name,seed", [("tum", 1000), ("kitti", 1001), ("euroc", 1002), ("kitti", 77)])
+def test_extraction_equals_compiled_reference(configs, name, seed):
+    w, h, nf, sfac, nl, ini, mn = configs[name]
+    img = synth.textured_frame(w, h, seed)
+    er = R.Extractor(nf, sfac, nl, ini, mn)
+    kr, dr = er.extract(img)
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    kg, dg = ex(img)
+    for l in range(nl):
+        assert np.array_equal(ex.pyramid_level(l), er.level_image(l)), ("pyramid", l)
+    _compare(kg, dg, kr, dr)
+    t = er.tables()
+    assert np.array_equal(ex.GetScaleFactors(), t["scale"]) and np.array_equal(ex.GetInverseScaleSigmaSquares(), t["inv_sigma2"])
+    assert np.array_equal(ex.GetFeaturesPerLevel(), t["nfeat"])
+
+
+@pytest.mark.parametrize("shape,params", [
+    ((200, 150), (300, 1.2, 6, 20, 7)),
+    ((333, 517), (500, 1.3, 5, 15, 5)),
+    ((1000, 90), (400, 1.2, 4, 12, 7)),
+    ((641, 479), (5000, 1.2, 8, 20, 7)),
+    ((640, 480), (40, 1.2, 8, 20, 7)),
+    ((1241, 376), (100, 1.2, 8, 20, 7)),   # wide image + small quota: more nodes than N after the first split
+    ((1241, 376), (40, 1.2, 8, 20, 7)),
+])
+def test_edge_shapes_equal_compiled_reference(shape, params):
+    w, h = shape
+    img = synth.textured_frame(w, h, 77)
+    kr, dr = R.Extractor(*params).extract(img)
+    kg, dg = orbb200.ORBextractor(*params)(img)
+    _compare(kg, dg, kr, dr)
+
+
+def test_4k_equals_compiled_reference():
+    """BASELINE config 4 at full size against the reference itself"""
+    img = synth.textured_frame(3840, 2160, 4)
+    kr, dr = R.Extractor(8000, 1.2, 12, 20, 7).extract(img)
+    kg, dg = orbb200.ORBextractor(8000, 1.2, 12, 20, 7)(img)
+    _compare(kg, dg, kr, dr)
+
+
+@pytest.mark.parametrize("seed", [1001, 1107])
+def test_stereo_frame_equals_compiled_reference(configs, seed):
+    """BASELINE config 2 against the reference's own stereo Frame constructor (Frame.cc:65-125): both extractions,
+    ComputeStereoMatches (mvuRight / mvDepth bit-exact) and the grid the windowed searches walk."""
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    left, right = synth.stereo_pair(w, h, seed)
+    bf, fx = 386.1448, 718.856
+    f = R.RefFrame(left, right, nf, sfac, nl, ini, mn, cam=(fx, fx, 607.1928, 185.2157), dist=(0, 0, 0, 0), bf=bf)
+    kL, dL = f.keys(0)
+    kR, dR = f.keys(1)
+    exL, exR = orbb200.ORBextractor(nf, sfac, nl, ini, mn), orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    gL, gdL = exL(left)
+    gR, gdR = exR(right)
+    _compare(gL, gdL, kL, dL)
+    _compare(gR, gdR, kR, dR)
+    b = float(np.float32(bf) / np.float32(fx))
+    uR, depth, nvalid = orbb200.stereo_match(exL, exR, bf, b)
+    ruR, rdepth = f.stereo()
+    same_desc = not (gdL != dL).any() and not (gdR != dR).any()
+    if same_desc:  # a flipped descriptor bit (allowed for <= 0.1 % of rows) may legitimately move one stereo match
+        assert np.array_equal(uR, ruR) and np.array_equal(depth, rdepth)
+    else:
+        assert (uR != ruR).sum() <= 4
+    assert (ruR >= 0).sum() > 100
+    # windowed search on the reference frame's own grid: candidates in GetFeaturesInArea order + distances
+    kU, _ = f.keys(2)
+    rng = np.random.default_rng(seed)
+    nq = 200
+    windows = np.zeros((nq, 5), np.float32)
+    windows[:, 0] = rng.uniform(-10, w + 10, nq)
+    windows[:, 1] = rng.uniform(-10, h + 10, nq)
+    windows[:, 2] = rng.choice([5.0, 15.0, 40.0], nq)
+    lv = [(-1, -1), (0, 2), (2, -1), (-1, 3), (1, 1)]
+    for q in range(nq):
+        windows[q, 3], windows[q, 4] = lv[q % 5]
+    qd = dL[rng.integers(0, len(dL), nq)]
+    minX, maxX, minY, maxY, iw, ih = [float(v) for v in f.bounds]
+    offs, cand, dist = orbb200.ORBmatcher().window_search(kU, dL, (minX, minY, iw, ih, 64, 48), windows, qd)
+    for q in range(nq):
+        want = f.features_in_area(float(windows[q, 0]), float(windows[q, 1]), float(windows[q, 2]), int(windows[q, 3]), int(windows[q, 4]))
+        got = cand[offs[q]:offs[q + 1]]
+        assert np.array_equal(got, want), q
+        for c in range(offs[q], min(offs[q + 1], offs[q] + 5)):
+            assert int(dist[c]) == R.descriptor_distance(qd[q], dL[cand[c]])
+
+
+def test_distinctive_descriptors_equal_compiled_reference():
+    import distinct_cases as dcases
+    m = orbb200.ORBmatcher()
+    for name in dcases.CASES:
+        desc, offs = dcases.case(name)
+        out, has = R.distinctive_descriptors(desc, offs)
+        gi, gm = m.distinctive_descriptors(desc, offs)
+        for g in range(len(offs) - 1):
+            if offs[g + 1] > offs[g]:
+                assert has[g] and np.array_equal(out[g], desc[offs[g] + gi[g]]), (name, g)
+            else:
+                assert gi[g] == -1 and not has[g]
