@@ -71,7 +71,12 @@ struct World {
     std::vector<KeyFrame *> kfs;
     std::vector<MapPoint *> mps;
     std::map<MapPoint *, long> idx;
-    explicit World(unsigned long long seed) : r(seed)
+    // MapPoint::mObservations is a std::map keyed by KeyFrame POINTER and ComputeDistinctiveDescriptors (called by Replace) keeps the
+    // first of several equally good rows in that order: keyframes are placement-constructed in one block so that their address
+    // order is their creation order in both twin worlds
+    enum { MAX_KFS = 8 };
+    void *kfBlock;
+    explicit World(unsigned long long seed) : r(seed), kfBlock(::operator new(sizeof(KeyFrame) * MAX_KFS))
     {
         db = new KeyFrameDatabase(voc);
         Frame::fx = FX; Frame::fy = FY; Frame::cx = CX; Frame::cy = CY; Frame::invfx = 1.0f / FX; Frame::invfy = 1.0f / FY;
@@ -83,7 +88,8 @@ struct World {
     ~World()
     {
         for (MapPoint *p : mps) delete p;
-        for (KeyFrame *k : kfs) delete k;
+        for (KeyFrame *k : kfs) k->~KeyFrame();
+        ::operator delete(kfBlock);
         for (Frame *f : frames) delete f;
         delete db;
     }
@@ -135,7 +141,8 @@ struct World {
     KeyFrame *keyframe(Frame *F)
     {
         regrid(F);
-        KeyFrame *K = new KeyFrame(*F, &map, db); // KeyFrame.cc:31-56: copies keys, descriptors, grid, pose
+        if (kfs.size() >= MAX_KFS) abort();
+        KeyFrame *K = new ((KeyFrame *)kfBlock + kfs.size()) KeyFrame(*F, &map, db); // KeyFrame.cc:31-56: copies keys, descriptors, grid, pose
         kfs.push_back(K);
         return K;
     }
