@@ -262,7 +262,7 @@ def run_b200(args, rank, world, local_rank):
 
     # ---- roofline of the dominant kernel (per-stage CUDA-event time inside the timed region)
     stage_ms = {k: v / max(ncalls, 1) for k, v in stage_sum.items()}
-    # the blur runs on a side stream beside FAST / quadtree, so the stage times overlap: stereo = step - whole extraction
+    # all stages run back to back on the handle's stream: stereo = step - whole extraction (first launch to last)
     extract_ms = ex.extract_total_ms_sum / max(ncalls, 1)
     stage_ms["stereo_match"] = max(ms_per_step - extract_ms, 0.0) if ncalls == args.steps else None
     stage_ms["extract_first_to_last_launch"] = extract_ms

@@ -114,9 +114,8 @@ int orbb200_extractor_sync(orbb200_extractor *e);
 /* per-stage device time of the LAST extract call, measured with CUDA events on the handle's stream when
  * profiling is enabled (off by default; the events serialise nothing but add ~1 us per stage).
  * stages: 0 pyramid, 1 fast_cells, 2 octree_select, 3 blur7, 4 orient_describe; with n >= 6 also 5 = the whole
- * extraction, first launch to last.  Each stage is timed by its own event pair on the stream it is launched on: the
- * blur of a monolithic device-resident batch runs on a side stream beside fast_cells / octree_select, so the five
- * stage times can add up to more than ms[5]. */
+ * extraction, first launch to last.  Each stage is timed by its own event pair on the handle's stream; the stages run
+ * back to back on that one stream, so the five stage times add up to ms[5] (up to event overhead). */
 int orbb200_extractor_set_profiling(orbb200_extractor *e, int on);
 int orbb200_extractor_stage_ms(orbb200_extractor *e, float *ms, int n);
 /* sum of the per-stage times over the calls recorded since profiling was switched on (at most the last 64);

@@ -64,12 +64,9 @@ struct orbb200_extractor {
     int profiling = 0;
     static constexpr int EV_RING = 64;
     // ring of per-call stage event sets, created when profiling is switched on: 0 start, 1 pyramid done, 2 FAST done,
-    // 3 quadtree done, 4 describe start (after the blur join), 5 describe done, 6 / 7 blur start / done (side stream)
+    // 3 quadtree done, 4 describe start, 5 describe done, 6 / 7 blur start / done
     static constexpr int EV_N = 8;
     cudaEvent_t ev[EV_RING][EV_N] = {};
-    // the blur of a monolithic device-resident batch runs on a side stream beside FAST / quadtree (it only needs the pyramid)
-    cudaStream_t sideStream = nullptr;
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
     int evCount = 0;                 // calls recorded since profiling was enabled
 };
 

@@ -4,7 +4,7 @@
 #include <stdarg.h>
 
 #include <algorithm>
-#include <chrono>
+#include <mutex>
 #include <new>
 #include <stdlib.h>
 
@@ -42,11 +42,32 @@ static short sat_short(int v) { return (short)std::min(32767, std::max(-32768, v
 
 // Per-shape geometry: pyramid sizes (:1351-1353), 30-px cell grid (:934-951), quadtree roots (:627-629),
 // cv::resize coefficient tables, workspace offsets.
+// MaxDynamicSharedMemorySize is an attribute of the FUNCTION (per device), not of a handle: the reference runs its left and right
+// extractor on two host threads, so every kernel with dynamic shared memory is opted in ONCE per device to the 200 KB the size
+// checks of this file allow, instead of being re-set to a per-launch size before every launch.
+static int opt_in_shared_memory(int device)
+{
+    static std::mutex mu;
+    static bool done[64] = {};
+    std::lock_guard<std::mutex> lk(mu);
+    if (device < 0 || device >= 64 || done[device]) return ORBB200_OK;
+    const int kMax = 200 * 1024;
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_pyramid_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_cells2, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    done[device] = true;
+    return ORBB200_OK;
+}
+
 int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
 {
     const bool sameShape = (w == e->w && h == e->h);
     if (sameShape && batch <= e->batchCap) return ORBB200_OK;
     ORB_CUDA_OK(cudaStreamSynchronize(e->stream));
+    {
+        const int rc = opt_in_shared_memory(e->device);
+        if (rc) return rc;
+    }
     const int L = e->nlevels;
     if (!sameShape) {
         size_t imgOff = 0, candOff = 0, wsOff = 0;

@@ -1,6 +1,7 @@
 // orbb200_match.cu -- C-ABI of the matcher searches (include/orbb200.h) over match_kernels.cuh / stereo_kernel.cuh.
 // Mirrors the arithmetic of ORB_SLAM2::ORBmatcher (reference src/ORBmatcher.cc) on POD arrays; the
 // MapPoint / KeyFrame bookkeeping of the Search* methods stays in the C++ facade (include/orbb200/ORBmatcher.h).
+#include <mutex>
 #include <algorithm>
 #include <vector>
 

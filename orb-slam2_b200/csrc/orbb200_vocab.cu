@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include "vocab_kernel.cuh"
@@ -34,7 +35,6 @@ struct orbb200_vocabulary {
     double *h_bowVal = nullptr;
     unsigned long long *h_fvKey = nullptr;
     int foldCap = 0, foldImgs = 0;
-    int foldSmemOptIn = 0;
 };
 
 namespace orbb200 {
@@ -146,6 +146,20 @@ static bool must_normalize(int scoring, int *norm)
 } // namespace orbb200
 
 using namespace orbb200;
+
+// MaxDynamicSharedMemorySize belongs to the function (per device), not to a vocabulary handle: opt k_bow_fold in once per device to
+// the 200 KB that the 8192-feature limit of the fold kernel needs, so that handles with different sizes cannot lower it under
+// one another
+static int fold_opt_in(int device)
+{
+    static std::mutex mu;
+    static bool done[64] = {};
+    std::lock_guard<std::mutex> lk(mu);
+    if (device < 0 || device >= 64 || done[device]) return ORBB200_OK;
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_bow_fold, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    done[device] = true;
+    return ORBB200_OK;
+}
 
 extern "C" {
 
@@ -358,10 +372,7 @@ int orbb200_compute_bow_batch(orbb200_vocabulary *v, const uint8_t *desc, const 
     if (!rc) rc = vocab_ensure_fold(v, n, nimg);
     if (rc) return rc;
     if (nimg == 0) return ORBB200_OK;
-    if ((int)smem > v->foldSmemOptIn) {
-        if (smem > 48 * 1024) ORB_CUDA_OK(cudaFuncSetAttribute(k_bow_fold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        v->foldSmemOptIn = (int)smem;
-    }
+    { const int rc2 = fold_opt_in(v->device); if (rc2) return rc2; }
     v->h_imgOff[0] = 0;
     for (int i = 0; i < nimg; i++) v->h_imgOff[i + 1] = v->h_imgOff[i] + counts[i];
     cudaStream_t st = v->stream;
@@ -433,10 +444,7 @@ int orbb200_compute_bow_batch_device(orbb200_vocabulary *v, const uint8_t *desc_
     const int n = nimg * cap;
     int rc = vocab_ensure_staging(v, n); // per-feature (word, weight, node) scratch
     if (rc) return rc;
-    if ((int)smem > v->foldSmemOptIn) {
-        if (smem > 48 * 1024) ORB_CUDA_OK(cudaFuncSetAttribute(k_bow_fold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        v->foldSmemOptIn = (int)smem;
-    }
+    { const int rc2 = fold_opt_in(v->device); if (rc2) return rc2; }
     cudaStream_t st = stream ? (cudaStream_t)stream : v->stream;
     rc = vocab_launch(v, desc_d, n, levelsup, v->d_word, v->d_w, v->d_nid, st, n_d, cap);
     if (rc) return rc;

@@ -290,7 +290,7 @@ class ORBextractor:
         ms = np.zeros(6, np.float32)
         n = C.c_int()
         check(self.L.orbb200_extractor_stage_ms_sum(self.h, _p(ms), 6, C.byref(n)))
-        self.extract_total_ms_sum = float(ms[5])  # first launch to last; the stages may overlap (blur on a side stream)
+        self.extract_total_ms_sum = float(ms[5])  # first launch to last (the stages run back to back on one stream)
         return dict(zip(self.STAGES, ms[:5].tolist())), n.value
 
     def last_launches(self):
