@@ -19,6 +19,10 @@ struct Scratch {
     cudaStream_t stream = nullptr;
     void *buf[12] = {};
     size_t cap[12] = {};
+    // the per-chunk partial top-2 buffer (slot 5) is shared by every brute-force search of this host thread, also by searches on
+    // different caller streams: the event orders each search behind the previous user of the buffer
+    cudaEvent_t partialDone = nullptr;
+    bool partialUsed = false;
 };
 static thread_local Scratch g_scratch;
 
@@ -30,6 +34,8 @@ static int scratch_bind(int device)
     if (s.device != device) {
         for (int i = 0; i < 12; i++) { s.buf[i] = nullptr; s.cap[i] = 0; } // buffers of another device are leaked on purpose
         s.stream = nullptr;
+        s.partialDone = nullptr;
+        s.partialUsed = false;
         s.device = device;
     }
     if (!s.stream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
@@ -67,12 +73,19 @@ static int bf_launch(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, o
     int groups, chunks, rows;
     bf_plan(nq, ndb, &groups, &chunks, &rows);
     void *partial;
-    int rc = scratch_get(5, sizeof(orbb200_top2) * (size_t)chunks * nq, &partial);
+    Scratch &sc = g_scratch;
+    if (!sc.partialDone) ORB_CUDA_OK(cudaEventCreateWithFlags(&sc.partialDone, cudaEventDisableTiming));
+    const size_t need = sizeof(orbb200_top2) * (size_t)chunks * nq;
+    if (sc.partialUsed && sc.cap[5] < need) ORB_CUDA_OK(cudaEventSynchronize(sc.partialDone)); // regrow: the last search may still read it
+    int rc = scratch_get(5, need, &partial);
     if (rc) return rc;
+    if (sc.partialUsed) ORB_CUDA_OK(cudaStreamWaitEvent(st, sc.partialDone, 0)); // previous search (any stream) is done with the buffer
     k_bf_top2<false><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb, rows, indexOffset, (orbb200_top2 *)partial,
                                                                   ExchangeParams());
     k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>((const orbb200_top2 *)partial, chunks, nq, out_d);
     ORB_CUDA_OK(cudaGetLastError());
+    ORB_CUDA_OK(cudaEventRecord(sc.partialDone, st));
+    sc.partialUsed = true;
     return ORBB200_OK;
 }
 

@@ -38,6 +38,31 @@ def test_bruteforce_top2_equals_oracle(nq, ndb):
     _eq(t, ref_cpu.bf_top2(q, db))
 
 
+def test_bruteforce_two_streams_from_one_thread():
+    """two device-resident searches issued back to back from one host thread on two different caller streams share the
+    thread's partial top-2 buffer: the second is ordered behind the first and both results equal the oracle"""
+    import torch
+    dev = torch.device("cuda", 0)
+    L = orbb200.lib()
+    q1, db1, _ = synth.descriptor_db(512, 60000, seed=3)
+    q2, db2, _ = synth.descriptor_db(512, 90000, seed=4)
+    tq1, tdb1 = torch.from_numpy(q1).to(dev), torch.from_numpy(db1).to(dev)
+    tq2, tdb2 = torch.from_numpy(q2).to(dev), torch.from_numpy(db2).to(dev)
+    o1 = torch.empty((512, 4), dtype=torch.int32, device=dev)
+    o2 = torch.empty((512, 4), dtype=torch.int32, device=dev)
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    torch.cuda.synchronize()
+    for rep in range(3):
+        orbb200.check(L.orbb200_match_bruteforce_top2_device(tq1.data_ptr(), 512, tdb1.data_ptr(), len(db1), o1.data_ptr(), 0, s1.cuda_stream))
+        orbb200.check(L.orbb200_match_bruteforce_top2_device(tq2.data_ptr(), 512, tdb2.data_ptr(), len(db2), o2.data_ptr(), 0, s2.cuda_stream))
+    torch.cuda.synchronize()
+    r1, r2 = ref_cpu.bf_top2(q1, db1), ref_cpu.bf_top2(q2, db2)
+    for o, r in ((o1, r1), (o2, r2)):
+        g = o.cpu().numpy()
+        assert np.array_equal(g[:, 0], r["best_dist"]) and np.array_equal(g[:, 1], r["best_idx"])
+        assert np.array_equal(g[:, 2], r["second_dist"]) and np.array_equal(g[:, 3], r["second_idx"])
+
+
 def test_bruteforce_all_equal_rows_first_index_wins():
     db = np.zeros((3000, 32), np.uint8)
     q = np.zeros((10, 32), np.uint8)
