@@ -34,7 +34,7 @@ struct LevelGeom {
 struct ExtractParams {
     int nlevels, batch, iniTh, minTh;
     const LevelGeom *geom;
-    const uint4 *fastCells; // two uint4 per grid cell (all levels): ROI, image slot, output slot (orbb200_extract.cu)
+    const uint4 *fastStrips; // FS_REC uint4 per FAST strip (all levels): ROI, image slot, cells, output slot (orbb200_extract.cu)
     const uint8_t *l0; // level 0: caller's image (device API) or the level-0 slot of pyr (host API)
     size_t l0ImgStride;
     int l0Pitch, l0Valid;
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_pyramid_resize(const __grid_cons
 }
 
 // E7 blur7: see blur_kernel.cuh
-// E3+E4 fast_cells: see fast_kernel.cuh
+// E3+E4 FAST per grid cell: see fast_strip_kernel.cuh
 
 #endif // ORBB200_EXTRACT_IMPL
 

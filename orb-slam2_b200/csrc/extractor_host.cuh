@@ -20,10 +20,11 @@ struct orbb200_extractor {
     size_t pyrStride = 0, candStride = 0, nodeWsStride = 0;
     int totalCells = 0, nodeTotal = 0, totalBlurTiles = 0, coefTotal = 0;
     size_t octreeSmem = 0;
-    int fastRows = 7; // staged ROI rows of the largest cell (k_fast_cells dynamic shared memory)
+    int fastRows = 7; // staged ROI rows of the tallest cell row (k_fast_strips dynamic shared memory)
+    int totalStrips = 0;
     // device buffers
     orbb200::LevelGeom *d_geom = nullptr;
-    uint4 *d_fastCells = nullptr;
+    uint4 *d_fastStrips = nullptr;
     int *d_umax = nullptr;
     int *d_rzXofs = nullptr, *d_rzYofs = nullptr;
     short2 *d_rzXa = nullptr, *d_rzYb = nullptr;

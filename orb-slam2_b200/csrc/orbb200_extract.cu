@@ -12,8 +12,7 @@
 #include "blur_kernel.cuh"
 #include "describe_kernel.cuh"
 #include "extractor_host.cuh"
-#include "fast_kernel.cuh"
-#include "fast2_kernel.cuh"
+#include "fast_strip_kernel.cuh"
 #include "stage_kernel.cuh"
 #include "octree_kernel.cuh"
 
@@ -53,7 +52,7 @@ static int opt_in_shared_memory(int device)
     if (device < 0 || device >= 64 || done[device]) return ORBB200_OK;
     const int kMax = 200 * 1024;
     ORB_CUDA_OK(cudaFuncSetAttribute(k_pyramid_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
-    ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_cells2, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     done[device] = true;
     return ORBB200_OK;
@@ -129,7 +128,7 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
         e->octreeSmem = octSmem;
         e->fastRows = 7;
         for (int l = 0; l < L; l++)
-            if (e->geom[l].nCells > 0) e->fastRows = std::min(std::max(e->fastRows, e->geom[l].hCell + 6), (int)FC_MAXROWS);
+            if (e->geom[l].nCells > 0) e->fastRows = std::min(std::max(e->fastRows, e->geom[l].hCell + 6), (int)FS_MAXROWS);
         if (octSmem > 200 * 1024) { set_error("nfeatures too large for the quadtree kernel's shared memory (%zu B)", octSmem); return ORBB200_ERR_ARG; }
         // cv::resize INTER_LINEAR tables (scale = 1/((double)dst/src), 11-bit coefficients)
         std::vector<int> xofs(coefOff, 0), yofs(coefOff, 0);
@@ -173,28 +172,62 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
         }
         if (dev_alloc(&e->d_geom, L)) return ORBB200_ERR_CUDA;
         {
-            // per-cell records of k_fast_cells: the ROI of src/ORBextractor.cc:953-985 for every cell of every level,
-            // worked out once per shape so that a block starts with one 32-byte load instead of a level search
-            std::vector<uint4> cells((size_t)2 * std::max(e->totalCells, 1), make_uint4(0, 0, 0, 0));
+            // strip records of k_fast_strips (fast_strip_kernel.cuh): the cell ROIs of src/ORBextractor.cc:953-985, worked out once
+            // per shape.  A strip = one cell row x a run of cells whose interiors add up to <= FS_MAXIW pixels; the cells the
+            // reference skips (:957-976) trail a row (or fill a skipped row) and only get their counts zeroed.
+            std::vector<uint4> strips;
             for (int l = 0; l < L; l++) {
                 const LevelGeom &g = e->geom[l];
+                if (g.nCells == 0) continue;
                 const int maxBX = g.w - 16, maxBY = g.h - 16;
-                for (int cc = 0; cc < g.nCells; cc++) {
-                    const int ci = cc / g.nCols, cj = cc - ci * g.nCols;
-                    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
-                    const int maxY = std::min(iniY + g.hCell + 6, maxBY), maxX = std::min(iniX + g.wCell + 6, maxBX);
-                    int rw = maxX - iniX, rh = maxY - iniY;
-                    if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || rw < 7 || rh < 7) rw = rh = 0; // skipped cell (:957-976)
-                    const int chunks = rw ? ((((maxX - (iniX & ~15)) + 15) & ~15) >> 4) : 1;
-                    uint4 &r0 = cells[(size_t)2 * (g.cellBase + cc)], &r1 = cells[(size_t)2 * (g.cellBase + cc) + 1];
-                    r0 = make_uint4((unsigned)iniX | ((unsigned)iniY << 16), (unsigned)rw | ((unsigned)rh << 16), g.imgOff,
-                                    (unsigned)g.pitch | ((unsigned)g.w << 16));
-                    r1 = make_uint4(g.candOff + (unsigned)cc * g.cellCap, (unsigned)(cj * g.wCell + 3) | ((unsigned)(ci * g.hCell + 3) << 12),
-                                    (unsigned)l, (65536u + chunks - 1) / chunks);
+                int nActCols = 0;
+                for (int cj = 0; cj < g.nCols; cj++) {
+                    const int iniX = 16 + cj * g.wCell;
+                    if (iniX >= maxBX - 6 || std::min(iniX + g.wCell + 6, maxBX) - iniX < 7) break;
+                    nActCols++;
+                }
+                // cells per strip: a bound-pass trip is one row x 32 pixel pairs, so the strip width with the fewest idle lanes in its
+                // last trip wins (ties: the wider strip, whose fixed costs are spread over more pixels)
+                const int perStripMax = std::max(1, FS_MAXIW / g.wCell);
+                int perStripBest = 1;
+                double bestEff = -1;
+                for (int C = 1; C <= perStripMax; C++) {
+                    const int ppr = (C * g.wCell + 1) / 2;
+                    const double eff = (double)ppr / (32.0 * div_up(ppr, 32));
+                    if (eff >= bestEff - 0.02) { bestEff = std::max(bestEff, eff); perStripBest = C; }
+                }
+                const int perStrip = perStripBest;
+                for (int ci = 0; ci < g.nRows; ci++) {
+                    const int iniY = 16 + ci * g.hCell, maxY = std::min(iniY + g.hCell + 6, maxBY);
+                    const bool rowActive = !(iniY >= maxBY - 3) && (maxY - iniY) >= 7 && nActCols > 0;
+                    for (int j0 = 0; j0 < g.nCols;) {
+                        int nAct = 0, nAll;
+                        if (rowActive && j0 < nActCols) {
+                            nAct = std::min(perStrip, nActCols - j0);
+                            nAll = nAct;
+                            if (j0 + nAct == nActCols) nAll = std::min(g.nCols - j0, 255); // the skipped cells that trail the row
+                        } else {
+                            nAll = std::min(g.nCols - j0, 255);
+                        }
+                        const int iniX = 16 + j0 * g.wCell;
+                        const int maxX = nAct ? std::min(iniX + nAct * g.wCell + 6, maxBX) : iniX;
+                        const int rw = nAct ? maxX - iniX : 0, rh = nAct ? maxY - iniY : 0;
+                        const int chunks = rw ? ((((maxX - (iniX & ~15)) + 15) & ~15) >> 4) : 1;
+                        if (rw - 6 > FS_MAXIW || chunks > FS_SPW / 8) { set_error("internal: FAST strip too wide (%d px)", rw); return ORBB200_ERR_ARG; }
+                        strips.push_back(make_uint4((unsigned)iniX | ((unsigned)iniY << 16), (unsigned)rw | ((unsigned)rh << 16), g.imgOff,
+                                                    (unsigned)g.pitch | ((unsigned)g.w << 16)));
+                        strips.push_back(make_uint4(g.candOff + (unsigned)(ci * g.nCols + j0) * g.cellCap,
+                                                    (unsigned)(j0 * g.wCell + 3) | ((unsigned)(ci * g.hCell + 3) << 12),
+                                                    (unsigned)l | ((unsigned)nAct << 4) | ((unsigned)nAll << 8) | ((unsigned)g.wCell << 16), 0u));
+                        strips.push_back(make_uint4((unsigned)(g.cellBase + ci * g.nCols + j0), (unsigned)g.cellCap, (65536u + chunks - 1) / chunks, 0u));
+                        j0 += nAll;
+                    }
                 }
             }
-            if (dev_alloc(&e->d_fastCells, cells.size())) return ORBB200_ERR_CUDA;
-            ORB_CUDA_OK(cudaMemcpy(e->d_fastCells, cells.data(), sizeof(uint4) * cells.size(), cudaMemcpyHostToDevice));
+            e->totalStrips = (int)(strips.size() / FS_REC);
+            if (strips.empty()) strips.assign(FS_REC, make_uint4(0, 0, 0, 0));
+            if (dev_alloc(&e->d_fastStrips, strips.size())) return ORBB200_ERR_CUDA;
+            ORB_CUDA_OK(cudaMemcpy(e->d_fastStrips, strips.data(), sizeof(uint4) * strips.size(), cudaMemcpyHostToDevice));
         }
         if (dev_alloc(&e->d_rzXofs, coefOff) || dev_alloc(&e->d_rzYofs, coefOff) || dev_alloc(&e->d_rzXa, coefOff) ||
             dev_alloc(&e->d_rzYb, coefOff))
