@@ -107,6 +107,19 @@ int orbb200_extract_batch_device(orbb200_extractor *e, const uint8_t *imgs_d, in
 int orbb200_pyramid_level(orbb200_extractor *e, int image_index, int level, uint8_t *dst, int dst_stride, int *w,
                           int *h);
 
+/* mvImagePyramid in ONE copy: the un-blurred levels of an image live in one device slab (level l at offsets[l], rows pitches[l]
+ * bytes apart, widths[l] x heights[l] pixels); orbb200_pyramid_download copies the slab of image `image_index` of the last call to
+ * dst (slab_bytes bytes) with a single D2H transfer -- what the facade's lazy mvImagePyramid does on first access. */
+int orbb200_pyramid_layout(orbb200_extractor *e, int *offsets, int *pitches, int *widths, int *heights, size_t *slab_bytes);
+int orbb200_pyramid_download(orbb200_extractor *e, int image_index, uint8_t *dst, size_t dst_bytes);
+/* same, into a pinned buffer owned by the handle (full-speed copy); *host_slab stays valid until the next orbb200_pyramid_map call
+ * on this handle or its destruction */
+int orbb200_pyramid_map(orbb200_extractor *e, int image_index, const uint8_t **host_slab);
+
+/* single-image calls (orbb200_extract / orbb200_extract_color) replay a CUDA graph captured per (shape, capacity): pinned bounce
+ * buffers, one graph launch, one synchronisation.  on = 0 sends them through the batch pipeline instead (A/B measurements). */
+int orbb200_extractor_set_graph(orbb200_extractor *e, int on);
+
 /* cudaStream_t of the handle (as void*), so callers can order their own work / events against it. */
 void *orbb200_extractor_stream(orbb200_extractor *e);
 int orbb200_extractor_sync(orbb200_extractor *e);

@@ -42,14 +42,44 @@
 #endif
 namespace ORBB200_NAMESPACE {
 
+class ORBextractor;
+
+/* mvImagePyramid, lazily: the levels stay on the device until somebody reads them (Frame::ComputeStereoMatches does,
+ * src/Frame.cc:584,674,691; orbb200::ComputeStereoMatches does not).  The first access after an extraction fetches the image's
+ * whole pyramid slab with ONE device-to-host copy; the cv::Mat of level l is a header over that host slab (rows `pitch` bytes
+ * apart, like the reference's ROI-of-a-bordered-image levels, src/ORBextractor.cc:1358-1360).  Indexing, size(), begin()/end()
+ * and conversion to const std::vector<cv::Mat>& cover every use the reference makes of the member. */
+class LazyPyramid {
+public:
+    LazyPyramid() : owner_(nullptr), stale_(false) {}
+    size_t size() const { return levels_.size(); }
+    bool empty() const { return levels_.empty(); }
+    void resize(size_t n) { levels_.resize(n); }
+    cv::Mat &operator[](size_t l) { sync(); return levels_[l]; }
+    const cv::Mat &operator[](size_t l) const { sync(); return levels_[l]; }
+    cv::Mat &at(size_t l) { sync(); return levels_.at(l); }
+    const cv::Mat &at(size_t l) const { sync(); return levels_.at(l); }
+    std::vector<cv::Mat>::const_iterator begin() const { sync(); return levels_.begin(); }
+    std::vector<cv::Mat>::const_iterator end() const { sync(); return levels_.end(); }
+    operator const std::vector<cv::Mat> &() const { sync(); return levels_; }
+    bool resident_on_host() const { return !stale_; } /* false: the levels of the last extraction have not been downloaded */
+
+private:
+    friend class ORBextractor;
+    inline void sync() const;
+    ORBextractor *owner_;
+    mutable bool stale_;
+    mutable std::vector<cv::Mat> levels_;
+};
+
 class ORBextractor {
 public:
     enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
-    enum PyramidMode { PYRAMID_EAGER = 0, PYRAMID_NONE = 1 };
+    enum PyramidMode { PYRAMID_LAZY = 0, PYRAMID_EAGER = 1, PYRAMID_NONE = 2 }; /* LAZY: one D2H on first read; EAGER: at the end of operator() */
 
     ORBextractor(int nfeatures_, float scaleFactor_, int nlevels_, int iniThFAST_, int minThFAST_)
         : nfeatures(nfeatures_), scaleFactor(scaleFactor_), nlevels(nlevels_), iniThFAST(iniThFAST_), minThFAST(minThFAST_),
-          handle_(nullptr), device_(-1), pyramidMode_(PYRAMID_EAGER)
+          handle_(nullptr), device_(-1), pyramidMode_(PYRAMID_LAZY)
     {
         static_assert(sizeof(cv::KeyPoint) == sizeof(orbb200_keypoint), "cv::KeyPoint must be the 28-byte POD");
         mvScaleFactor.resize(nlevels);
@@ -62,6 +92,7 @@ public:
                                          mvLevelSigma2.data(), mvInvLevelSigma2.data(), mnFeaturesPerLevel.data(), umax.data()))
             std::cerr << "ORBextractor: " << orbb200_last_error() << std::endl;
         mvImagePyramid.resize(nlevels);
+        mvImagePyramid.owner_ = this;
     }
 
     ~ORBextractor() { orbb200_extractor_destroy(handle_); } /* the reference never deletes its extractors; harmless */
@@ -93,7 +124,7 @@ public:
             cv::Mat d = _descriptors.getMat();
             for (int i = 0; i < n; i++) std::memcpy(d.ptr(i), descBuf_.data() + (size_t)i * 32, 32);
         }
-        if (pyramidMode_ == PYRAMID_EAGER) download_pyramid();
+        pyramid_ready();
     }
 
     /* Extension: the cv::cvtColor prologue of Tracking::GrabImage* (src/Tracking.cc:177-202, 218-231, 255-266)
@@ -122,7 +153,7 @@ public:
             cv::Mat d = _descriptors.getMat();
             for (int i = 0; i < n; i++) std::memcpy(d.ptr(i), descBuf_.data() + (size_t)i * 32, 32);
         }
-        if (pyramidMode_ == PYRAMID_EAGER) download_pyramid();
+        pyramid_ready();
         if (imGray) {
             int w = 0, h = 0;
             imGray->create(imColor.rows, imColor.cols, CV_8UC1);
@@ -137,7 +168,7 @@ public:
     std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
     std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
-    std::vector<cv::Mat> mvImagePyramid;
+    LazyPyramid mvImagePyramid;
 
     /* ---- extensions -------------------------------------------------------------------------------- */
     void SetDevice(int device) { device_ = device; }
@@ -156,14 +187,27 @@ protected:
         std::cerr << "ORBextractor (orbb200): " << msg << std::endl;
         d.release();
     }
+    friend class LazyPyramid;
+    /* after an extraction: mark the host copy stale (LAZY), refresh it now (EAGER), or leave it alone (NONE) */
+    void pyramid_ready()
+    {
+        mvImagePyramid.stale_ = pyramidMode_ != PYRAMID_NONE;
+        if (pyramidMode_ == PYRAMID_EAGER) mvImagePyramid.sync();
+    }
+    /* one device-to-host copy of the last image's pyramid slab; level headers over it */
     void download_pyramid()
     {
-        for (int l = 0; l < nlevels; l++) {
-            int w = 0, h = 0;
-            if (orbb200_pyramid_level(handle_, 0, l, nullptr, 0, &w, &h)) return;
-            mvImagePyramid[l].create(h, w, CV_8UC1);
-            orbb200_pyramid_level(handle_, 0, l, mvImagePyramid[l].data, (int)mvImagePyramid[l].step, &w, &h);
+        if (!handle_) return;
+        int offs[ORBB200_MAX_LEVELS], pit[ORBB200_MAX_LEVELS], ws[ORBB200_MAX_LEVELS], hs[ORBB200_MAX_LEVELS];
+        size_t bytes = 0;
+        if (orbb200_pyramid_layout(handle_, offs, pit, ws, hs, &bytes) != ORBB200_OK) return;
+        const uint8_t *slab = nullptr; /* pinned, owned by the handle: valid until the next download */
+        if (orbb200_pyramid_map(handle_, 0, &slab) != ORBB200_OK) {
+            std::cerr << "ORBextractor (orbb200): " << orbb200_last_error() << std::endl;
+            return;
         }
+        for (int l = 0; l < nlevels; l++)
+            mvImagePyramid.levels_[l] = cv::Mat(hs[l], ws[l], CV_8UC1, const_cast<uint8_t *>(slab) + offs[l], (size_t)pit[l]);
     }
 
     int nfeatures;
@@ -183,6 +227,13 @@ protected:
     PyramidMode pyramidMode_;
     std::vector<unsigned char> descBuf_;
 };
+
+inline void LazyPyramid::sync() const
+{
+    if (!stale_ || !owner_) return;
+    stale_ = false;
+    owner_->download_pyramid();
+}
 
 } // namespace ORBB200_NAMESPACE (ORB_SLAM2 by default)
 

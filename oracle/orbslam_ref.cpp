@@ -263,6 +263,56 @@ int oref_frame_pyramid_level(void *h, int right, int level, int *w, int *hgt, un
     return oref_pyramid_level(right ? o->eR : o->eL, level, w, hgt, out);
 }
 
+/* ---- timing sessions (bench.py --impl reference / cpu_baseline kind "reference") -------------------------------------------
+   What Tracking::GrabImageStereo does per frame pair with its two persistent extractors (src/Tracking.cc:124-127, 177-213): the
+   stereo Frame constructor = ExtractORB of both images on two threads + UndistortKeyPoints + ComputeStereoMatches + grid. */
+struct OrefSession {
+    ORBextractor *eL, *eR;
+    cv::Mat K, D;
+    float bf, thDepth;
+    void *buf;
+};
+void *oref_session_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, const float *cam, float bf, float thDepth)
+{
+    OrefSession *s = new OrefSession;
+    s->eL = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    s->eR = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    s->K = cv::Mat::eye(3, 3, CV_32F);
+    s->K.at<float>(0, 0) = cam[0]; s->K.at<float>(1, 1) = cam[1]; s->K.at<float>(0, 2) = cam[2]; s->K.at<float>(1, 2) = cam[3];
+    s->D = cv::Mat::zeros(4, 1, CV_32F);
+    s->bf = bf; s->thDepth = thDepth;
+    s->buf = ::operator new(sizeof(Frame));
+    return s;
+}
+void oref_session_destroy(void *h)
+{
+    OrefSession *s = (OrefSession *)h;
+    delete s->eL; delete s->eR;
+    ::operator delete(s->buf);
+    delete s;
+}
+/* one stereo pair (imR != NULL) or one monocular frame; returns N, *nStereo = keypoints with a stereo match */
+int oref_session_frame(void *h, const unsigned char *imL, const unsigned char *imR, int w, int hgt, int *nStereo)
+{
+    OrefSession *s = (OrefSession *)h;
+    cv::Mat L(hgt, w, CV_8UC1, (void *)imL, (size_t)w);
+    memset(s->buf, 0, sizeof(Frame));
+    const float mb = s->bf / s->K.at<float>(0, 0); /* see oref_frame_create: mb is read before the constructor assigns it */
+    memcpy((char *)s->buf + (size_t)((char *)&((Frame *)s->buf)->mb - (char *)s->buf), &mb, sizeof(float));
+    Frame *F;
+    if (imR) {
+        cv::Mat R(hgt, w, CV_8UC1, (void *)imR, (size_t)w);
+        F = new (s->buf) Frame(L, R, 0.0, s->eL, s->eR, (ORBVocabulary *)0, s->K, s->D, s->bf, s->thDepth);
+    } else
+        F = new (s->buf) Frame(L, 0.0, s->eL, (ORBVocabulary *)0, s->K, s->D, s->bf, s->thDepth);
+    const int n = F->N;
+    int ns = 0;
+    for (size_t i = 0; i < F->mvuRight.size(); i++) ns += F->mvuRight[i] >= 0;
+    if (nStereo) *nStereo = ns;
+    F->~Frame();
+    return n;
+}
+
 /* A Frame built from caller-supplied keypoints / descriptors (no extraction): UndistortKeyPoints is the identity
    (k1 = 0 path is not even entered: mvKeysUn is set directly), AssignFeaturesToGrid is the reference's (Frame.cc:261-279)
    with the bounds supplied by the caller the way ComputeImageBounds leaves them for an undistorted image. */

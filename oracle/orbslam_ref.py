@@ -51,6 +51,11 @@ def lib():
         l.oref_frame_pyramid_level.argtypes = [vp, i, i, vp, vp, vp]
         l.oref_frame_from_keys.restype = vp
         l.oref_frame_from_keys.argtypes = [vp, vp, i, i, i, f, i]
+        l.oref_session_create.restype = vp
+        l.oref_session_create.argtypes = [i, f, i, i, i, vp, f, f]
+        l.oref_session_destroy.argtypes = [vp]
+        l.oref_session_frame.restype = i
+        l.oref_session_frame.argtypes = [vp, vp, vp, i, i, vp]
         l.oref_distinctive_descriptors.restype = i
         l.oref_distinctive_descriptors.argtypes = [vp, vp, i, vp, vp]
         l.oref_descriptor_distance.restype = i
@@ -199,6 +204,28 @@ class RefFrame:
         out = np.zeros((h.value, w.value), np.uint8)
         self.L.oref_frame_pyramid_level(self.h, int(right), l, C.byref(w), C.byref(h), _p(out))
         return out
+
+
+class Session:
+    """persistent extractor pair + the reference's stereo / mono Frame constructor per call (timing arm of bench.py)"""
+
+    def __init__(self, nfeatures=2000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, cam=(718.856, 718.856, 607.1928, 185.2157),
+                 bf=386.1448, th_depth=35.0):
+        self.L = lib()
+        cam = np.asarray(cam, np.float32)
+        self.h = self.L.oref_session_create(nfeatures, scale_factor, nlevels, ini_th, min_th, _p(cam), bf, th_depth)
+
+    def __del__(self):
+        try:
+            self.L.oref_session_destroy(self.h)
+        except Exception:
+            pass
+
+    def frame(self, imL, imR=None):
+        h, w = imL.shape
+        ns = C.c_int(0)
+        n = self.L.oref_session_frame(self.h, _p(imL), _p(imR), w, h, C.byref(ns))
+        return n, ns.value
 
 
 def distinctive_descriptors(desc, offsets):

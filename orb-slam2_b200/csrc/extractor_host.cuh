@@ -52,6 +52,16 @@ struct orbb200_extractor {
     uint8_t *d_stage[PIPE_STAGES] = {};
     size_t stageBytes = 0;
     int pipeChunk = 16, pipeStreams = 8, devChunk = 0;
+    // single-image latency path (orbb200_extract): pinned bounce buffers + the whole launch sequence (H2D, level-0 staging,
+    // pyramid, FAST, quadtree, blur, describe, D2H) captured once per (shape, capacity) in a CUDA graph
+    uint8_t *h_in = nullptr, *h_out = nullptr, *d_in1 = nullptr;
+    size_t hInBytes = 0, hOutBytes = 0, dIn1Bytes = 0;
+    uint8_t *h_pyr = nullptr; // pinned copy of one image's pyramid slab (orbb200_pyramid_map)
+    size_t hPyrBytes = 0;
+    cudaGraphExec_t graph1 = nullptr;
+    int graphW = 0, graphH = 0, graphCap = 0, graphCh = 0, graphRFirst = 0;
+    unsigned long long graphEpoch = 0, allocEpoch = 1; // allocEpoch moves whenever a device buffer the graph points at is reallocated
+    int useGraph = 1;
     // last call
     int lastBatch = 0, lastCap = 0;
     const uint8_t *lastL0 = nullptr;

@@ -251,6 +251,7 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
         dev_alloc(&e->d_lvlKp, (size_t)e->nodeTotal * B) || dev_alloc(&e->d_lvlCount, (size_t)L * B))
         return ORBB200_ERR_CUDA;
     e->batchCap = batch;
+    e->allocEpoch++;
     return ORBB200_OK;
 }
 

@@ -17,7 +17,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
 
 EXPORTS = [
-    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity",
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity", "orbb200_pyramid_layout", "orbb200_pyramid_download", "orbb200_pyramid_map", "orbb200_extractor_set_graph",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
@@ -59,6 +59,10 @@ def lib():
     L.orbb200_max_keypoints.argtypes = [vp]
     L.orbb200_max_keypoints_for_shape.argtypes = [vp, ip, ip]
     L.orbb200_last_capacity.argtypes = [vp]
+    L.orbb200_pyramid_layout.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbb200_pyramid_download.argtypes = [vp, ip, vp, sz]
+    L.orbb200_pyramid_map.argtypes = [vp, ip, vp]
+    L.orbb200_extractor_set_graph.argtypes = [vp, ip]
     L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch_device.argtypes = [vp, vp, ip, ip, ip, ip, sz, vp, vp, ip, vp]
@@ -276,6 +280,19 @@ class ORBextractor:
 
     def set_pipeline(self, chunk_images, compute_streams, device_chunk_images=0):
         check(self.L.orbb200_extractor_set_pipeline(self.h, int(chunk_images), int(compute_streams), int(device_chunk_images)))
+
+    def set_graph(self, on):
+        check(self.L.orbb200_extractor_set_graph(self.h, int(on)))
+
+    def pyramid(self, image_index=0):
+        """all un-blurred levels of one image of the last call from ONE device-to-host copy of its slab"""
+        n = self.nlevels
+        offs, pit, ws, hs = (np.zeros(n, np.int32) for _ in range(4))
+        nb = C.c_size_t(0)
+        check(self.L.orbb200_pyramid_layout(self.h, _p(offs), _p(pit), _p(ws), _p(hs), C.byref(nb)))
+        slab = np.zeros(nb.value, np.uint8)
+        check(self.L.orbb200_pyramid_download(self.h, image_index, _p(slab), nb.value))
+        return [slab[offs[l]:offs[l] + pit[l] * hs[l]].reshape(hs[l], pit[l])[:, :ws[l]] for l in range(n)]
 
     def set_profiling(self, on):
         check(self.L.orbb200_extractor_set_profiling(self.h, int(on)))

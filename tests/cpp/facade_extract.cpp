@@ -1,6 +1,8 @@
 // facade_extract.cpp -- drives the C++ facade (include/orbb200/ORBextractor.h) exactly like Frame::ExtractORB does
 // (reference src/Frame.cc:285-292, 73-79) and dumps the results for tests/test_gpu_facade.py.
 //   facade_extract <w> <h> <nfeat> <scale> <nlevels> <ini> <min> <left.raw> <right.raw|-> <out_prefix> [bf b]
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -56,9 +58,63 @@ static int color_main(int argc, char **argv)
     return 0;
 }
 
+// Latency of the drop-in's real call pattern (src/Frame.cc:285-292: one image per call; :82-85: left and right on two host threads):
+//   facade_extract --latency <w> <h> <nfeat> <nlevels> <left.raw> <right.raw|-> <iters> <graph 0|1>
+// prints one JSON object: p50 / p99 / mean microseconds of ORBextractor::operator() (mono) or of the two-thread pair (stereo),
+// mvImagePyramid left on the device (lazy) -- plus the cost of the first pyramid read.
+static int latency_main(int argc, char **argv)
+{
+    if (argc < 10) return 2;
+    const int w = atoi(argv[2]), h = atoi(argv[3]), nfeat = atoi(argv[4]), nlevels = atoi(argv[5]);
+    const bool stereo = std::string(argv[7]) != "-";
+    const int iters = atoi(argv[8]), graph = atoi(argv[9]);
+    cv::Mat imLeft(h, w, CV_8UC1), imRight(h, w, CV_8UC1);
+    if (!read_raw(argv[6], imLeft)) return 3;
+    if (stereo && !read_raw(argv[7], imRight)) return 3;
+    ORBextractor exL(nfeat, 1.2f, nlevels, 20, 7), exR(nfeat, 1.2f, nlevels, 20, 7);
+    orbb200_extractor_set_graph(exL.Handle(), graph);
+    orbb200_extractor_set_graph(exR.Handle(), graph);
+    std::vector<cv::KeyPoint> kL, kR;
+    cv::Mat dL, dR;
+    std::vector<double> us;
+    double pyrUs = 0;
+    size_t n = 0;
+    for (int it = -20; it < iters; it++) { // 20 warm-up calls (graph capture, allocations)
+        const auto t0 = std::chrono::steady_clock::now();
+        if (stereo) {
+            std::thread tl([&] { exL(imLeft, cv::Mat(), kL, dL); });
+            std::thread tr([&] { exR(imRight, cv::Mat(), kR, dR); });
+            tl.join();
+            tr.join();
+        } else {
+            exL(imLeft, cv::Mat(), kL, dL);
+        }
+        const auto t1 = std::chrono::steady_clock::now();
+        if (it >= 0) us.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+        n = kL.size();
+        if (it == iters - 1) {
+            if (exL.mvImagePyramid.resident_on_host()) { fprintf(stderr, "lazy pyramid was downloaded without being read\n"); return 4; }
+            const auto p0 = std::chrono::steady_clock::now();
+            const int rows = exL.mvImagePyramid[nlevels - 1].rows;
+            pyrUs = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - p0).count();
+            if (rows <= 0 || !exL.mvImagePyramid.resident_on_host()) return 4;
+        }
+    }
+    std::sort(us.begin(), us.end());
+    double mean = 0;
+    for (double v : us) mean += v;
+    mean /= us.size();
+    printf("{\"call\": \"%s\", \"shape\": \"%dx%d\", \"nfeatures\": %d, \"graph\": %d, \"iters\": %d, \"p50_us\": %.1f, \"p99_us\": %.1f, "
+           "\"mean_us\": %.1f, \"min_us\": %.1f, \"keypoints\": %zu, \"first_pyramid_read_us\": %.1f}\n",
+           stereo ? "ORBextractor::operator() x2, two host threads (Frame.cc:82-85)" : "ORBextractor::operator()", w, h, nfeat, graph, iters,
+           us[us.size() / 2], us[std::min(us.size() - 1, (size_t)(us.size() * 0.99))], mean, us[0], n, pyrUs);
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
     if (argc > 1 && std::string(argv[1]) == "--color") return color_main(argc, argv);
+    if (argc > 1 && std::string(argv[1]) == "--latency") return latency_main(argc, argv);
     if (argc < 11) { fprintf(stderr, "usage\n"); return 2; }
     const int w = atoi(argv[1]), h = atoi(argv[2]), nfeat = atoi(argv[3]);
     const float scale = (float)atof(argv[4]);

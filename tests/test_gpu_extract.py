@@ -205,3 +205,37 @@ def test_pipeline_settings_do_not_change_results(configs):
                 assert np.array_equal(kd[b, :n[b]], kps0[b, :n[b]].view(np.uint8).reshape(-1, 28)), (pitch, chunk, ns, b)
                 assert np.array_equal(desc_d[b, :n[b]].cpu().numpy(), desc0[b, :n[b]]), (pitch, chunk, ns, b)
             assert np.array_equal(uR, st0[0]) and np.array_equal(nv, st0[2]), (pitch, chunk, ns)
+
+
+def test_single_image_graph_path_equals_batch_pipeline(configs):
+    """orbb200_extract replays a CUDA graph per (shape, capacity); results must equal the batch pipeline's (graph off), also
+    when shapes alternate (re-capture), for the colour prologue, and the lazy pyramid slab must equal the per-level copies"""
+    rng_shapes = [("tum", 1000), ("kitti", 1001), ("tum", 1003)]
+    ex = orbb200.ORBextractor(1000, 1.2, 8, 20, 7)
+    for name, seed in rng_shapes:
+        w, h = configs[name][0], configs[name][1]
+        img = synth.textured_frame(w, h, seed)
+        ex.set_graph(1)
+        k1, d1 = ex(img)
+        k1b, d1b = ex(img)  # second call replays the captured graph
+        pyr = ex.pyramid(0)
+        for l in range(8):
+            assert np.array_equal(pyr[l], ex.pyramid_level(l)), l
+        ex.set_graph(0)
+        k0, d0 = ex(img)
+        assert np.array_equal(k1, k0) and np.array_equal(d1, d0)
+        assert np.array_equal(k1b, k0) and np.array_equal(d1b, d0)
+    img = synth.textured_frame(640, 480, 5)
+    col = np.stack([img, img[::-1].copy(), img[:, ::-1].copy()], axis=2)
+    ex.set_graph(1)
+    kc1, dc1 = ex.extract_color(col, 1)
+    ex.set_graph(0)
+    kc0, dc0 = ex.extract_color(col, 1)
+    assert np.array_equal(kc1, kc0) and np.array_equal(dc1, dc0) and len(kc1) > 500
+    # a strided view (rows not contiguous) through the graph path
+    big = np.zeros((480, 700), np.uint8)
+    big[:, :640] = img
+    ex.set_graph(1)
+    ks, ds = ex(big[:, :640])
+    kr, dr = ref_cpu.RefExtractor(1000, 1.2, 8, 20, 7).extract(img)
+    _compare(ks, ds, kr, dr)
