@@ -18,7 +18,9 @@
 
 namespace orbb200 {
 
-constexpr int OCT_THREADS = 256, OCT_KU = 4; // threads per block, keys per thread per trip of the per-key loops
+constexpr int OCT_THREADS = 256; // threads per block
+constexpr int OCT_THREADS_BIG = 1024;      // large images (level 0 above 1 Mpixel, e.g. 4K: ~250 k candidates in one level): the per-key
+                                           // loops of a pass are L2-latency bound, four times the threads keep four times the keys in flight
 
 struct NodeBuf {
     int *x0, *x1, *y0, *y1, *cnt, *seq;
@@ -53,8 +55,9 @@ __device__ __forceinline__ int key_quadrant(uint32_t k, int xs, int ys)
 // shared memory: everything the two per-key loops of a pass touch per node -- quadrant counts cc 4C, child positions
 // 4C, new positions C, split coordinates recX / recY C each (recX < 0: node not split in this pass) -- + sort keys
 // (sortLen u64).  With the node arrays in global memory a key cost a chain of three dependent L2 loads per loop.
-__global__ void __launch_bounds__(OCT_THREADS, 6) k_octree_select(const __grid_constant__ ExtractParams P)
+template <int MAXT, int MINB> __global__ void __launch_bounds__(MAXT, MINB) k_octree_select(const __grid_constant__ ExtractParams P)
 {
+    constexpr int OCT_KU = 4; // keys per thread per trip of the per-key loops, all their loads in flight together (8 measured slower on 4K)
     extern __shared__ __align__(16) unsigned char dsm[];
     __shared__ int scanTmp[34];
     __shared__ int sh_size, sh_finish, sh_mode, sh_seq, sh_nexp, sh_rstar;

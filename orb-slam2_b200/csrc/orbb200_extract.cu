@@ -53,7 +53,8 @@ static int opt_in_shared_memory(int device)
     const int kMax = 200 * 1024;
     ORB_CUDA_OK(cudaFuncSetAttribute(k_pyramid_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
-    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS_BIG, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     done[device] = true;
     return ORBB200_OK;
 }
