@@ -116,6 +116,11 @@ int orbb200_pyramid_download(orbb200_extractor *e, int image_index, uint8_t *dst
  * on this handle or its destruction */
 int orbb200_pyramid_map(orbb200_extractor *e, int image_index, const uint8_t **host_slab);
 
+/* page-locked host memory for the buffers handed to the *_batch entry points (the dataset loader decodes straight into it):
+ * copies from pinned memory run at full PCIe speed and really overlap the kernels */
+int orbb200_host_alloc(void **p, size_t bytes);
+int orbb200_host_free(void *p);
+
 /* single-image calls (orbb200_extract / orbb200_extract_color) replay a CUDA graph captured per (shape, capacity): pinned bounce
  * buffers, one graph launch, one synchronisation.  on = 0 sends them through the batch pipeline instead (A/B measurements). */
 int orbb200_extractor_set_graph(orbb200_extractor *e, int on);

@@ -23,10 +23,35 @@ __device__ __forceinline__ Desc load_desc(const uint8_t *p)
     return d;
 }
 
+// full adder on 32 bit columns at once: sum = a ^ b ^ c, carry = majority(a, b, c) -- one LOP3 each
+__device__ __forceinline__ void csa(unsigned int a, unsigned int b, unsigned int c, unsigned int &sum, unsigned int &carry)
+{
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(sum) : "r"(a), "r"(b), "r"(c));
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(carry) : "r"(a), "r"(b), "r"(c));
+}
+
+// Hamming distance of two 256-bit rows.  The straight form is 8 XOR + 8 POPC; POPC issues at 16 lanes / clk / SM (a quarter of
+// the logic rate), which is what bounded the brute-force search (92 % of the POPC peak).  Three carry-save adders fold seven of the
+// eight XOR words into one word of weight 1 and three of weight 2: 5 POPC + 14 LOP3 per pair put the POPC pipe (10 clk per
+// warp-pair) and the ALU pipe (~10 clk) in balance.  (A fourth adder -> 4 POPC makes the ALU pipe the longer one again.)
 __device__ __forceinline__ int hamming(const Desc &a, const Desc &b)
 {
+#ifdef ORBB200_HAMMING_PLAIN
     return (__popc(a.lo.x ^ b.lo.x) + __popc(a.lo.y ^ b.lo.y)) + (__popc(a.lo.z ^ b.lo.z) + __popc(a.lo.w ^ b.lo.w)) +
            (__popc(a.hi.x ^ b.hi.x) + __popc(a.hi.y ^ b.hi.y)) + (__popc(a.hi.z ^ b.hi.z) + __popc(a.hi.w ^ b.hi.w));
+#else
+    unsigned int s0, c0, s1, c1, s2, c2;
+    csa(a.lo.x ^ b.lo.x, a.lo.y ^ b.lo.y, a.lo.z ^ b.lo.z, s0, c0);
+    csa(a.lo.w ^ b.lo.w, a.hi.x ^ b.hi.x, a.hi.y ^ b.hi.y, s1, c1);
+    csa(s0, s1, a.hi.z ^ b.hi.z, s2, c2);
+#ifdef ORBB200_HAMMING_4POPC
+    unsigned int s3, c3;
+    csa(c0, c1, c2, s3, c3);
+    return __popc(s2) + __popc(a.hi.w ^ b.hi.w) + 2 * __popc(s3) + 4 * __popc(c3);
+#else
+    return (__popc(s2) + __popc(a.hi.w ^ b.hi.w)) + 2 * (__popc(c0) + __popc(c1) + __popc(c2));
+#endif
+#endif
 }
 
 struct Top2 {
