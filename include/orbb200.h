@@ -201,6 +201,18 @@ int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt,
 int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int nt, const int *cand_offsets,
                                 const int *cand_idx, uint16_t *dist, int device);
 
+/* SearchForTriangulation resolved on the device (src/ORBmatcher.cc:757-815 with CheckDistEpipolarLine :147-164): for every query
+ * (descriptor q[i], undistorted position qxy[i] = {x, y}, qstereo[i] = mvuRight >= 0) over its CSR candidate list into the targets
+ * (t, tkp = mvKeysUn of keyframe 2, tstereo): the candidate with the smallest distance <= th_low that passes the epipole gate
+ * (both monocular: squared distance to (ex, ey) >= 100 * scale_factors[octave]) and the epipolar test
+ * ((a x2 + b y2 + c)^2 / (a^2 + b^2) < 3.84 * level_sigma2[octave], [a b c] = [x1 y1 1] F12), a later candidate winning ties.
+ * best_idx2[i] = target index or -1, best_dist[i] (may be NULL) its distance.  The callers' gates that do not depend on the
+ * distance (existing map points, bOnlyStereo) are applied when the lists are built. */
+int orbb200_search_triangulation(const uint8_t *q, const float *qxy, const uint8_t *qstereo, int nq, const uint8_t *t,
+                                 const orbb200_keypoint *tkp, const uint8_t *tstereo, int nt, const int *cand_offsets, const int *cand_idx,
+                                 const float *F12, float ex, float ey, const float *scale_factors, const float *level_sigma2, int nlevels,
+                                 int th_low, int *best_idx2, int *best_dist, int device);
+
 /* F3 + F2 + distances in one call: Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:261-279, 444-456) on the
  * target keypoints tkp[nt] (the caller's mvKeysUn; grid = mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv,
  * FRAME_GRID_COLS x FRAME_GRID_ROWS), then Frame::GetFeaturesInArea (:386-442) for every query window

@@ -426,27 +426,44 @@ public:
                 f2it = pKF2->mFeatVec.lower_bound(f1it->first);
             }
         }
-        std::vector<uint16_t> dist;
-        if (!distances(qDesc, (int)qIdx1.size(), pKF2->mDescriptors, offs, cand, dist)) { vMatchedPairs.clear(); return 0; }
-        // epilogue (:762-835): note `dist > bestDist` -- a later candidate at an equal distance replaces an earlier one
+        // ONE device call resolves every query (:757-815): distances, TH_LOW, the epipole gate and CheckDistEpipolarLine, a later
+        // candidate winning at equal distance.  (vbMatched2 is never set in this code base, so the queries are independent.)
+        const int nq = (int)qIdx1.size(), nt = pKF2->N;
+        std::vector<float> qxy((size_t)2 * nq), Ff(9);
+        std::vector<unsigned char> qst(nq), tst(nt > 0 ? nt : 1);
+        for (int q = 0; q < nq; q++) {
+            const cv::KeyPoint &kp1 = pKF1->mvKeysUn[qIdx1[q]];
+            qxy[2 * q] = kp1.pt.x; qxy[2 * q + 1] = kp1.pt.y;
+            qst[q] = pKF1->mvuRight[qIdx1[q]] >= 0 ? 1 : 0;
+        }
+        for (int i = 0; i < nt; i++) tst[i] = pKF2->mvuRight[i] >= 0 ? 1 : 0;
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) Ff[3 * r + c] = F12.template at<float>(r, c);
+        std::vector<int> best2(nq > 0 ? nq : 1, -1);
+        if (nq > 0) {
+            static_assert(sizeof(cv::KeyPoint) == sizeof(orbb200_keypoint), "cv::KeyPoint must be the 28-byte POD");
+            const cv::Mat &D2 = pKF2->mDescriptors;
+            std::vector<unsigned char> tpacked;
+            const unsigned char *tptr = D2.ptr(0);
+            if (!D2.isContinuous()) {
+                tpacked.resize((size_t)nt * 32);
+                for (int i = 0; i < nt; i++) std::memcpy(&tpacked[(size_t)i * 32], D2.ptr(i), 32);
+                tptr = tpacked.data();
+            }
+            const int rc = orbb200_search_triangulation(qDesc.data(), qxy.data(), qst.data(), nq, tptr,
+                                                        reinterpret_cast<const orbb200_keypoint *>(pKF2->mvKeysUn.data()), tst.data(), nt, offs.data(),
+                                                        cand.empty() ? nullptr : cand.data(), Ff.data(), ex, ey, pKF2->mvScaleFactors.data(),
+                                                        pKF2->mvLevelSigma2.data(), (int)pKF2->mvScaleFactors.size(), TH_LOW, best2.data(), nullptr, device_);
+            if (rc != ORBB200_OK) {
+                std::cerr << "ORBmatcher (orbb200): " << orbb200_last_error() << std::endl;
+                vMatchedPairs.clear();
+                return 0;
+            }
+        }
+        // epilogue (:816-835): matches, rotation histogram
         for (size_t q = 0; q < qIdx1.size(); q++) {
             const int idx1 = qIdx1[q];
-            const bool bStereo1 = pKF1->mvuRight[idx1] >= 0;
             const cv::KeyPoint &kp1 = pKF1->mvKeysUn[idx1];
-            int bestDist = TH_LOW, bestIdx2 = -1;
-            for (int c = offs[q]; c < offs[q + 1]; c++) {
-                const int idx2 = cand[c];
-                const int d = dist[c];
-                if (d > TH_LOW || d > bestDist) continue;
-                const cv::KeyPoint &kp2 = pKF2->mvKeysUn[idx2];
-                const bool bStereo2 = pKF2->mvuRight[idx2] >= 0;
-                if (!bStereo1 && !bStereo2) {
-                    const float distex = ex - kp2.pt.x;
-                    const float distey = ey - kp2.pt.y;
-                    if (distex * distex + distey * distey < 100 * pKF2->mvScaleFactors[kp2.octave]) continue;
-                }
-                if (CheckDistEpipolarLine(kp1, kp2, F12, pKF2)) { bestIdx2 = idx2; bestDist = d; }
-            }
+            const int bestIdx2 = best2[q];
             if (bestIdx2 >= 0) {
                 const cv::KeyPoint &kp2 = pKF2->mvKeysUn[bestIdx2];
                 vMatches12[idx1] = bestIdx2;

@@ -770,6 +770,42 @@ void ref_match_candidates(const uint8_t *q, int nq, const uint8_t *t, const int 
     }
 }
 
+/* ------------------------------------------------------------------------- */
+/* M8  the per-query loop of ORBmatcher::SearchForTriangulation                 */
+/*     src/ORBmatcher.cc:757-815 with CheckDistEpipolarLine :147-164            */
+/* candidates in list order; `dist > bestDist` continues, so a later candidate  */
+/* replaces an earlier one at equal distance; vbMatched2 is never set (:725).   */
+/* ------------------------------------------------------------------------- */
+void ref_search_triangulation(const uint8_t *q, const float *qxy, const uint8_t *qstereo, int nq, const uint8_t *t, const ref_keypoint *tkp,
+                              const uint8_t *tstereo, const int *offs, const int *idx, const float *F12, float ex, float ey,
+                              const float *sf, const float *sig2, int th_low, int *best_idx2, int *best_dist)
+{
+    for (int i = 0; i < nq; i++) {
+        const float x1 = qxy[2 * i], y1 = qxy[2 * i + 1];
+        const float a = x1 * F12[0] + y1 * F12[3] + F12[6];
+        const float b = x1 * F12[1] + y1 * F12[4] + F12[7];
+        const float c = x1 * F12[2] + y1 * F12[5] + F12[8];
+        int bestDist = th_low, bestIdx2 = -1;
+        for (int cc = offs[i]; cc < offs[i + 1]; cc++) {
+            const int i2 = idx[cc];
+            const int dist = ref_descriptor_distance(q + (size_t)i * 32, t + (size_t)i2 * 32);
+            if (dist > th_low || dist > bestDist) continue;
+            const ref_keypoint *kp2 = tkp + i2;
+            if (!qstereo[i] && !tstereo[i2]) {
+                const float distex = ex - kp2->x, distey = ey - kp2->y;
+                if (distex * distex + distey * distey < 100 * sf[kp2->octave]) continue;
+            }
+            const float num = a * kp2->x + b * kp2->y + c;
+            const float den = a * a + b * b;
+            if (den == 0) continue;
+            const float dsqr = num * num / den;
+            if (dsqr < 3.84 * sig2[kp2->octave]) { bestIdx2 = i2; bestDist = dist; }
+        }
+        best_idx2[i] = bestIdx2;
+        best_dist[i] = bestIdx2 >= 0 ? bestDist : -1;
+    }
+}
+
 /* accept test of the BoW searches (ORBmatcher.cc:242-244): best <= TH_LOW and best < ratio*second */
 int ref_ratio_accept(int best, int second, int th, float ratio)
 {

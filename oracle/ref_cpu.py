@@ -62,6 +62,7 @@ def lib():
     L.ref_descriptor_distance.argtypes = [vp, vp]
     L.ref_bf_top2.argtypes = [vp, ip, vp, ip, vp, ip]
     L.ref_match_candidates.argtypes = [vp, ip, vp, vp, vp, vp]
+    L.ref_search_triangulation.argtypes = [vp, vp, vp, ip, vp, vp, vp, vp, vp, vp, fp, fp, vp, vp, ip, vp, vp]
     L.ref_ratio_accept.restype = ip
     L.ref_distinctive_descriptors.argtypes = [vp, vp, ip, vp, vp]
     L.ref_ratio_accept.argtypes = [ip, ip, ip, fp]
@@ -187,6 +188,19 @@ def match_candidates(q, t, offs, idx):
     out = np.zeros(len(q), TOP2_DTYPE)
     lib().ref_match_candidates(_p(q), len(q), _p(t), _p(offs), _p(idx), _p(out))
     return out
+
+
+def search_triangulation(q, qxy, qstereo, t, tkp, tstereo, offs, idx, F12, ex, ey, sf, sig2, th_low=50):
+    q, t = np.ascontiguousarray(q, np.uint8), np.ascontiguousarray(t, np.uint8)
+    qxy = np.ascontiguousarray(qxy, np.float32)
+    qstereo, tstereo = np.ascontiguousarray(qstereo, np.uint8), np.ascontiguousarray(tstereo, np.uint8)
+    tkp = np.ascontiguousarray(tkp, KP_DTYPE)
+    offs, idx = np.ascontiguousarray(offs, np.int32), np.ascontiguousarray(idx, np.int32)
+    F12, sf, sig2 = np.ascontiguousarray(F12, np.float32), np.ascontiguousarray(sf, np.float32), np.ascontiguousarray(sig2, np.float32)
+    bi, bd = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
+    lib().ref_search_triangulation(_p(q), _p(qxy), _p(qstereo), len(q), _p(t), _p(tkp), _p(tstereo), _p(offs), _p(idx), _p(F12), ex, ey, _p(sf),
+                                   _p(sig2), th_low, _p(bi), _p(bd))
+    return bi, bd
 
 
 def distinctive_descriptors(desc, offsets):

@@ -371,6 +371,66 @@ __global__ void k_candidate_distances(const uint8_t *__restrict__ q, int nq, con
         dist[c] = (unsigned short)hamming(Q, load_desc(t + (size_t)__ldg(idx + c) * 32));
 }
 
+// ---------------------------------------------------------------------------------------------------
+// M8  SearchForTriangulation, resolved on the device (src/ORBmatcher.cc:757-815, CheckDistEpipolarLine :147-164).
+// In this code base vbMatched2 is never set (:725 / :773), so the queries are independent: per query the reference keeps the
+// candidate with the smallest distance <= TH_LOW among those that pass the epipole gate (:791-797) and the epipolar chi-square
+// test, a LATER candidate replacing an earlier one at equal distance (`dist > bestDist` continues, :784).  One warp per query:
+// lanes stride the CSR list in order with `<=`, the warp keeps (min distance, max position).  Float expressions in the
+// reference's order with explicit round-to-nearest operations (no FMA contraction); 3.84 * sigma2 is a double product (:163).
+// ---------------------------------------------------------------------------------------------------
+struct TriangulationParams {
+    float F[9];         // F12 row-major
+    float ex, ey;       // epipole of camera 1 in image 2
+    float sf[ORBB200_MAX_LEVELS], sig2[ORBB200_MAX_LEVELS];
+    int thLow;
+};
+
+__global__ void k_triangulation_search(const uint8_t *__restrict__ q, const float2 *__restrict__ qxy, const uint8_t *__restrict__ qstereo, int nq,
+                                       const uint8_t *__restrict__ t, const orbb200_keypoint *__restrict__ tkp, const uint8_t *__restrict__ tstereo,
+                                       const int *__restrict__ offs, const int *__restrict__ idx, const __grid_constant__ TriangulationParams P,
+                                       int *__restrict__ bestIdx2, int *__restrict__ bestDist)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= nq) return;
+    const Desc Q = load_desc(q + (size_t)warp * 32);
+    const float2 p1 = qxy[warp];
+    const bool st1 = qstereo[warp] != 0;
+    // epipolar line of kp1 in image 2: l = x1' F12 = [a b c] (:150-152)
+    const float a = __fadd_rn(__fadd_rn(__fmul_rn(p1.x, P.F[0]), __fmul_rn(p1.y, P.F[3])), P.F[6]);
+    const float b = __fadd_rn(__fadd_rn(__fmul_rn(p1.x, P.F[1]), __fmul_rn(p1.y, P.F[4])), P.F[7]);
+    const float c = __fadd_rn(__fadd_rn(__fmul_rn(p1.x, P.F[2]), __fmul_rn(p1.y, P.F[5])), P.F[8]);
+    const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+    const int c0 = offs[warp], c1 = offs[warp + 1];
+    int bd = P.thLow, bpos = -1;
+    for (int cc = c0 + lane; cc < c1; cc += 32) {
+        const int i2 = __ldg(idx + cc);
+        const int d = hamming(Q, load_desc(t + (size_t)i2 * 32));
+        if (d > P.thLow || d > bd) continue;
+        const orbb200_keypoint k2 = tkp[i2];
+        if (!st1 && tstereo[i2] == 0) {
+            const float dx = __fsub_rn(P.ex, k2.x), dy = __fsub_rn(P.ey, k2.y);
+            if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, P.sf[k2.octave])) continue;
+        }
+        const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, k2.x), __fmul_rn(b, k2.y)), c);
+        if (den == 0.f) continue;
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if (!((double)dsqr < 3.84 * (double)P.sig2[k2.octave])) continue;
+        bd = d;
+        bpos = cc;
+    }
+    // smallest distance, then the latest position
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const int od = __shfl_xor_sync(0xffffffffu, bd, o), op = __shfl_xor_sync(0xffffffffu, bpos, o);
+        if (op >= 0 && (bpos < 0 || od < bd || (od == bd && op > bpos))) { bd = od; bpos = op; }
+    }
+    if (lane == 0) {
+        bestIdx2[warp] = bpos >= 0 ? idx[bpos] : -1;
+        bestDist[warp] = bpos >= 0 ? bd : -1;
+    }
+}
+
 // POPC-pipe peak probe for the matching roofline: dependent-free popc chains, 8 per iteration.
 __global__ void k_popc_peak(unsigned int *out, int iters)
 {

@@ -230,6 +230,54 @@ int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int 
     return ORBB200_OK;
 }
 
+int orbb200_search_triangulation(const uint8_t *q, const float *qxy, const uint8_t *qstereo, int nq, const uint8_t *t,
+                                 const orbb200_keypoint *tkp, const uint8_t *tstereo, int nt, const int *cand_offsets, const int *cand_idx,
+                                 const float *F12, float ex, float ey, const float *scale_factors, const float *level_sigma2, int nlevels,
+                                 int th_low, int *best_idx2, int *best_dist, int device)
+{
+    if (nq <= 0) return ORBB200_OK;
+    ORB_ARG_OK(q && qxy && qstereo && cand_offsets && best_idx2 && F12 && scale_factors && level_sigma2, "null pointer");
+    ORB_ARG_OK(nlevels > 0 && nlevels <= ORBB200_MAX_LEVELS, "bad level count");
+    const int total = cand_offsets[nq];
+    if (total <= 0) {
+        ORB_ARG_OK(cand_offsets[0] == 0 && total == 0, "candidate offsets must start at 0");
+        for (int i = 0; i < nq; i++) { best_idx2[i] = -1; if (best_dist) best_dist[i] = -1; }
+        return ORBB200_OK;
+    }
+    ORB_ARG_OK(t && tkp && tstereo && cand_idx && nt > 0, "candidates without targets");
+    ORB_ARG_OK(csr_valid(cand_offsets, nq, cand_idx, nt), "candidate lists: offsets not ascending from 0 or index outside [0, nt)");
+    for (int i = 0; i < nt; i++) ORB_ARG_OK(tkp[i].octave >= 0 && tkp[i].octave < nlevels, "target keypoint octave outside the level tables");
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    void *dq, *dt, *dkp, *dts, *dqxy, *dqs, *doffs, *didx, *dbi, *dbd;
+    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)nt * 32, &dt)) ||
+        (rc = scratch_get(2, (size_t)nt * sizeof(orbb200_keypoint), &dkp)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
+        (rc = scratch_get(4, (size_t)total * 4, &didx)) || (rc = scratch_get(6, (size_t)nt, &dts)) || (rc = scratch_get(7, (size_t)nq * 8, &dqxy)) ||
+        (rc = scratch_get(8, (size_t)nq, &dqs)) || (rc = scratch_get(9, (size_t)nq * 4, &dbi)) || (rc = scratch_get(10, (size_t)nq * 4, &dbd)))
+        return rc;
+    cudaStream_t st = g_scratch.stream;
+    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dts, tstereo, (size_t)nt, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dqxy, qxy, (size_t)nq * 8, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(dqs, qstereo, (size_t)nq, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
+    TriangulationParams P;
+    memset(&P, 0, sizeof(P));
+    for (int i = 0; i < 9; i++) P.F[i] = F12[i];
+    P.ex = ex; P.ey = ey; P.thLow = th_low;
+    for (int l = 0; l < nlevels; l++) { P.sf[l] = scale_factors[l]; P.sig2[l] = level_sigma2[l]; }
+    k_triangulation_search<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, (const float2 *)dqxy, (const uint8_t *)dqs, nq, (const uint8_t *)dt,
+                                                                (const orbb200_keypoint *)dkp, (const uint8_t *)dts, (const int *)doffs,
+                                                                (const int *)didx, P, (int *)dbi, (int *)dbd);
+    ORB_CUDA_OK(cudaMemcpyAsync(best_idx2, dbi, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    if (best_dist) ORB_CUDA_OK(cudaMemcpyAsync(best_dist, dbd, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
 int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int nt, float minX, float minY, float invW, float invH,
                           int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets, int *cand_idx,
                           uint16_t *dist, int cand_cap, int device)

@@ -22,7 +22,7 @@ EXPORTS = [
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
-    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_window_search", "orbb200_merge_top2",
+    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_search_triangulation", "orbb200_window_search", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
     "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
     "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
@@ -82,6 +82,7 @@ def lib():
     L.orbb200_match_bruteforce_top2_device.argtypes = [vp, ip, vp, ip, vp, ip, vp]
     L.orbb200_match_candidates.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
     L.orbb200_candidate_distances.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
+    L.orbb200_search_triangulation.argtypes = [vp, vp, vp, ip, vp, vp, vp, ip, vp, vp, vp, fp, fp, vp, vp, ip, ip, vp, vp, ip]
     L.orbb200_window_search.argtypes = [vp, vp, ip, fp, fp, fp, fp, ip, ip, vp, vp, ip, vp, vp, vp, ip, ip]
     L.orbb200_merge_top2.argtypes = [vp, ip, ip, vp, ip]
     L.orbb200_merge_top2_device.argtypes = [vp, ip, ip, vp, vp]
@@ -379,6 +380,19 @@ class ORBmatcher:
         out = np.zeros(max(int(offsets[-1]), 1), np.uint16)
         check(self.L.orbb200_candidate_distances(_p(q), len(q), _p(t), len(t), _p(offsets), _p(idx), _p(out), self.device))
         return out[:int(offsets[-1])]
+
+    def search_triangulation(self, q, qxy, qstereo, t, tkp, tstereo, offs, idx, F12, ex, ey, sf, sig2, th_low=50):
+        """SearchForTriangulation resolved on the device (orbb200_search_triangulation): (best_idx2, best_dist) per query"""
+        q, t = np.ascontiguousarray(q, np.uint8), np.ascontiguousarray(t, np.uint8)
+        qxy = np.ascontiguousarray(qxy, np.float32)
+        qstereo, tstereo = np.ascontiguousarray(qstereo, np.uint8), np.ascontiguousarray(tstereo, np.uint8)
+        tkp = np.ascontiguousarray(tkp, KP_DTYPE)
+        offs, idx = np.ascontiguousarray(offs, np.int32), np.ascontiguousarray(idx, np.int32)
+        F12, sf, sig2 = np.ascontiguousarray(F12, np.float32), np.ascontiguousarray(sf, np.float32), np.ascontiguousarray(sig2, np.float32)
+        bi, bd = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
+        check(self.L.orbb200_search_triangulation(_p(q), _p(qxy), _p(qstereo), len(q), _p(t), _p(tkp), _p(tstereo), len(t), _p(offs), _p(idx), _p(F12),
+                                                  ex, ey, _p(sf), _p(sig2), len(sf), th_low, _p(bi), _p(bd), self.device))
+        return bi, bd
 
     def window_search(self, tkps, tdesc, grid, windows, qdesc, cap=None):
         """F3 + F2 + distances (orbb200_window_search).  grid = (minX, minY, invW, invH, cols, rows);

@@ -131,6 +131,43 @@ def test_candidate_distances_equal_oracle_and_reference():
             m.candidate_distances(q, t, bad_offs, idx)
 
 
+def test_search_triangulation_equals_oracle():
+    """orbb200_search_triangulation (k_triangulation_search): the whole per-query loop of SearchForTriangulation on the device --
+    distances, TH_LOW, epipole gate, CheckDistEpipolarLine, later-candidate-wins ties -- against the C restatement
+    (src/ORBmatcher.cc:757-815, 147-164) on keyframe-sized inputs (2 000 queries x ~50 candidates), incl. empty lists"""
+    rng = np.random.default_rng(33)
+    nq, nt = 2000, 2100
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    tkp = np.zeros(nt, orbb200.KP_DTYPE)
+    tkp["x"], tkp["y"] = rng.uniform(0, 640, nt).astype(np.float32), rng.uniform(0, 480, nt).astype(np.float32)
+    tkp["octave"] = rng.integers(0, 8, nt)
+    q = np.zeros((nq, 32), np.uint8)
+    qxy = np.zeros((nq, 2), np.float32)
+    sizes = rng.choice([0, 1, 20, 50, 64, 90], size=nq)
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    idx = rng.integers(0, nt, int(offs[-1])).astype(np.int32)
+    for i in range(nq):  # several candidates of a query are near copies at the SAME distance on the query's epipolar line (a row)
+        qxy[i] = (rng.uniform(0, 640), rng.uniform(20, 460))
+        q[i] = rng.integers(0, 256, 32, dtype=np.uint8)
+        for c in range(offs[i], offs[i + 1]):
+            if rng.random() < 0.35:
+                j = idx[c]
+                bits = np.unpackbits(q[i])
+                bits[rng.choice(256, int(rng.choice([3, 3, 10, 30, 60])), replace=False)] ^= 1
+                t[j] = np.packbits(bits)
+                tkp["y"][j] = qxy[i, 1] + np.float32(rng.normal(0, 1.5))
+    qst = (rng.random(nq) < 0.3).astype(np.uint8)
+    tst = (rng.random(nt) < 0.3).astype(np.uint8)
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) + rng.normal(0, 1e-4, (3, 3)).astype(np.float32)
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    sig2 = (sf * sf).astype(np.float32)
+    ex, ey = 300.5, 240.25
+    gi, gd = orbb200.ORBmatcher().search_triangulation(q, qxy, qst, t, tkp, tst, offs, idx, F12, ex, ey, sf, sig2)
+    ri, rd = ref_cpu.search_triangulation(q, qxy, qst, t, tkp, tst, offs, idx, F12, ex, ey, sf, sig2)
+    assert np.array_equal(gi, ri) and np.array_equal(gd, rd)
+    assert (ri >= 0).sum() > 300 and (ri[sizes == 0] == -1).all()
+
+
 def test_match_candidates_equals_oracle():
     rng = np.random.default_rng(9)
     nq, nt = 1500, 1800
