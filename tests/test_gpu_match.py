@@ -165,7 +165,7 @@ def test_search_triangulation_equals_oracle():
     gi, gd = orbb200.ORBmatcher().search_triangulation(q, qxy, qst, t, tkp, tst, offs, idx, F12, ex, ey, sf, sig2)
     ri, rd = ref_cpu.search_triangulation(q, qxy, qst, t, tkp, tst, offs, idx, F12, ex, ey, sf, sig2)
     assert np.array_equal(gi, ri) and np.array_equal(gd, rd)
-    assert (ri >= 0).sum() > 300 and (ri[sizes == 0] == -1).all()
+    assert (ri >= 0).sum() > 80 and (ri[sizes == 0] == -1).all()  # (targets are shared between lists: later queries overwrite planted copies)
 
 
 def test_match_candidates_equals_oracle():
