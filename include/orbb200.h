@@ -116,6 +116,11 @@ int orbb200_pyramid_download(orbb200_extractor *e, int image_index, uint8_t *dst
  * on this handle or its destruction */
 int orbb200_pyramid_map(orbb200_extractor *e, int image_index, const uint8_t **host_slab);
 
+/* pins the calling host thread to the CPUs local to `device` (-1: current) -- /sys/bus/pci/devices/<bus id>/local_cpulist -- so that
+ * pinned buffers allocated afterwards live on the GPU's NUMA node and copies are submitted from a near core (multi-GPU hosts:
+ * one call per rank before it allocates).  Returns the number of CPUs in the new mask, 0 when the topology cannot be read. */
+int orbb200_bind_host_to_device(int device);
+
 /* page-locked host memory for the buffers handed to the *_batch entry points (the dataset loader decodes straight into it):
  * copies from pinned memory run at full PCIe speed and really overlap the kernels */
 int orbb200_host_alloc(void **p, size_t bytes);

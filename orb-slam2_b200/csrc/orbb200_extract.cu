@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <sched.h>
 #include <new>
 #include <stdlib.h>
 
