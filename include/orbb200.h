@@ -242,6 +242,28 @@ int orbb200_window_search_device(const orbb200_keypoint *tkp_d, const uint8_t *t
                                  const uint8_t *qdesc_d, int nq, int *cand_offsets_d, int *cand_idx_d, uint16_t *dist_d,
                                  int cand_cap, int *workspace_d, void *stream);
 
+/* orbb200_window_search with the TARGET frame already resident on the device (tkp_d / tdesc_d = device pointers, e.g. the
+ * outputs of the extraction or a copy a host object keeps -- include/orbb200/DeviceFrame.h); windows, query descriptors and results
+ * are host buffers.  Only the queries travel: 52 bytes per window instead of 60 bytes per target keypoint per search. */
+int orbb200_window_search_resident(const orbb200_keypoint *tkp_d, const uint8_t *tdesc_d, int nt, float minX, float minY, float invW,
+                                   float invH, int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets,
+                                   int *cand_idx, uint16_t *dist, int cand_cap, int device);
+
+/* device pointers of the outputs of the LAST extraction on this handle (kps [image][cap], desc [image][cap][32], counts [image]);
+ * valid until the next extraction on the handle -- a frame that wants to keep them copies them (orbb200_copy_on_device) */
+int orbb200_extractor_outputs_device(orbb200_extractor *e, const orbb200_keypoint **kps_d, const uint8_t **desc_d, const int **n_out_d, int *cap);
+
+/* plain device-memory helpers for host-side objects that keep data resident; all synchronous */
+int orbb200_device_alloc(void **p, size_t bytes, int device);
+int orbb200_device_free(void *p);
+int orbb200_copy_to_device(void *dst_d, const void *src, size_t bytes);
+int orbb200_copy_to_host(void *dst, const void *src_d, size_t bytes);
+int orbb200_copy_on_device(void *dst_d, const void *src_d, size_t bytes);
+/* bytes the matcher entry points (and orbb200_copy_to_device) have copied host -> device so far, process-wide */
+unsigned long long orbb200_h2d_bytes_total(void);
+/* cudaDeviceSynchronize on `device` (-1: current): orders work issued on caller streams before the library's own streams */
+int orbb200_device_sync(int device);
+
 /* merge of per-shard top-2 results (config 5, database sharded by rows; shard s's indices already global):
  * parts[s*nq + i]; ties on best_dist go to the lowest shard (= lowest global index, first-seen rule). */
 int orbb200_merge_top2(const orbb200_top2 *parts, int nshards, int nq, orbb200_top2 *out, int device);

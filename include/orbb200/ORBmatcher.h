@@ -37,6 +37,7 @@
 #include "cv_shim.h"
 #endif
 #include "../orbb200.h"
+#include "DeviceFrame.h"
 
 /* The classes live in ORB_SLAM2 so that the reference's callers compile unchanged.  A test that links the reference's own
    classes of the same name beside these (tests/cpp/ref_match.cpp) renames the namespace with -DORBB200_NAMESPACE=... */
@@ -1092,9 +1093,18 @@ protected:
 #else
         const int cols = 64, rows = 48;
 #endif
+        // a frame that keeps its extraction outputs on the device (member `orbb200::DeviceFrame *mpDeviceFrame`): nothing of the
+        // frame is uploaded, only the windows and the query descriptors travel
+        orbb200::DeviceFrame *df = device_frame_of(F, 0);
+        if (df && df->N() == (int)F.mvKeysUn.size()) {
+            df->SetGrid(F.mnMinX, F.mnMinY, F.mfGridElementWidthInv, F.mfGridElementHeightInv, cols, rows);
+            return df->WindowSearch(windows, qDesc, offs, cand, dist);
+        }
         return window_search(F.mvKeysUn, F.mDescriptors, F.mnMinX, F.mnMinY, F.mfGridElementWidthInv, F.mfGridElementHeightInv,
                              cols, rows, windows, qDesc, offs, cand, dist);
     }
+    template <class T> static auto device_frame_of(const T &F, int) -> decltype(F.mpDeviceFrame) { return F.mpDeviceFrame; }
+    template <class T> static orbb200::DeviceFrame *device_frame_of(const T &, long) { return nullptr; }
 
     bool window_search(const std::vector<cv::KeyPoint> &tkps, const cv::Mat &targets, float minX, float minY, float invW, float invH,
                        int cols, int rows, const std::vector<float> &windows, const std::vector<unsigned char> &qDesc,

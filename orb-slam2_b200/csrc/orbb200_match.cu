@@ -1,6 +1,7 @@
 // orbb200_match.cu -- C-ABI of the matcher searches (include/orbb200.h) over match_kernels.cuh / stereo_kernel.cuh.
 // Mirrors the arithmetic of ORB_SLAM2::ORBmatcher (reference src/ORBmatcher.cc) on POD arrays; the
 // MapPoint / KeyFrame bookkeeping of the Search* methods stays in the C++ facade (include/orbb200/ORBmatcher.h).
+#include <atomic>
 #include <mutex>
 #include <algorithm>
 #include <vector>
@@ -25,6 +26,11 @@ struct Scratch {
     bool partialUsed = false;
 };
 static thread_local Scratch g_scratch;
+
+// bytes this translation unit's entry points copied host -> device (descriptor / keypoint / query uploads of the searches): lets a
+// test prove that a device-resident frame is searched without re-uploading its descriptors (orbb200_h2d_bytes_total)
+static std::atomic<unsigned long long> g_h2dBytes(0);
+static inline void count_h2d(size_t bytes) { g_h2dBytes.fetch_add((unsigned long long)bytes); }
 
 static int scratch_bind(int device)
 {
@@ -223,6 +229,7 @@ int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int 
     ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
     ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
     ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
+    count_h2d((size_t)nq * 36 + (size_t)nt * 32 + (size_t)total * 4);
     k_candidate_distances<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
                                                                (const int *)didx, (unsigned short *)dout);
     ORB_CUDA_OK(cudaMemcpyAsync(dist, dout, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
@@ -264,6 +271,7 @@ int orbb200_search_triangulation(const uint8_t *q, const float *qxy, const uint8
     ORB_CUDA_OK(cudaMemcpyAsync(dqs, qstereo, (size_t)nq, cudaMemcpyHostToDevice, st));
     ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
     ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
+    count_h2d((size_t)nq * 45 + (size_t)nt * 61 + (size_t)total * 4);
     TriangulationParams P;
     memset(&P, 0, sizeof(P));
     for (int i = 0; i < 9; i++) P.F[i] = F12[i];
@@ -278,9 +286,11 @@ int orbb200_search_triangulation(const uint8_t *q, const float *qxy, const uint8
     return ORBB200_OK;
 }
 
-int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int nt, float minX, float minY, float invW, float invH,
-                          int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets, int *cand_idx,
-                          uint16_t *dist, int cand_cap, int device)
+// host queries / host results; the targets (keypoints + descriptors) either come from the host (uploaded here) or are already
+// resident on the device (orbb200_window_search_resident: a frame that keeps its extraction outputs in HBM)
+static int window_search_impl(const orbb200_keypoint *tkp, const uint8_t *tdesc, bool resident, int nt, float minX, float minY, float invW,
+                              float invH, int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets,
+                              int *cand_idx, uint16_t *dist, int cand_cap, int device)
 {
     ORB_ARG_OK(cand_offsets != nullptr, "cand_offsets is null");
     for (int i = 0; i <= std::max(nq, 0); i++) cand_offsets[i] = 0;
@@ -296,10 +306,18 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
         (rc = scratch_get(3, (size_t)(nq + 1) * 4, &dcnt)))
         return rc;
     cudaStream_t st = g_scratch.stream;
-    ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dtd, tdesc, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+    if (resident) {
+        ORB_ARG_OK(((size_t)tdesc & 15) == 0, "resident descriptors must be 16-byte aligned");
+        dkp = const_cast<orbb200_keypoint *>(tkp);
+        dtd = const_cast<uint8_t *>(tdesc);
+    } else {
+        ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
+        ORB_CUDA_OK(cudaMemcpyAsync(dtd, tdesc, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+        count_h2d((size_t)nt * (sizeof(orbb200_keypoint) + 32));
+    }
     ORB_CUDA_OK(cudaMemcpyAsync(dwin, windows, (size_t)nq * 20, cudaMemcpyHostToDevice, st));
     ORB_CUDA_OK(cudaMemcpyAsync(dqd, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    count_h2d((size_t)nq * 52);
     WindowParams W;
     memset(&W, 0, sizeof(W));
     W.G.kp = (const orbb200_keypoint *)dkp; W.G.n = nt;
@@ -326,6 +344,68 @@ int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int
     ORB_CUDA_OK(cudaMemcpyAsync(cand_idx, dcand, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_OK(cudaMemcpyAsync(dist, ddist, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    return ORBB200_OK;
+}
+
+int orbb200_window_search(const orbb200_keypoint *tkp, const uint8_t *tdesc, int nt, float minX, float minY, float invW, float invH,
+                          int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets, int *cand_idx,
+                          uint16_t *dist, int cand_cap, int device)
+{
+    return window_search_impl(tkp, tdesc, false, nt, minX, minY, invW, invH, cols, rows, windows, qdesc, nq, cand_offsets, cand_idx, dist, cand_cap,
+                              device);
+}
+
+int orbb200_window_search_resident(const orbb200_keypoint *tkp_d, const uint8_t *tdesc_d, int nt, float minX, float minY, float invW,
+                                   float invH, int cols, int rows, const float *windows, const uint8_t *qdesc, int nq, int *cand_offsets,
+                                   int *cand_idx, uint16_t *dist, int cand_cap, int device)
+{
+    return window_search_impl(tkp_d, tdesc_d, true, nt, minX, minY, invW, invH, cols, rows, windows, qdesc, nq, cand_offsets, cand_idx, dist,
+                              cand_cap, device);
+}
+
+/* ---- plain device-memory helpers for host objects that keep data resident (include/orbb200/DeviceFrame.h) ---- */
+int orbb200_device_alloc(void **p, size_t bytes, int device)
+{
+    ORB_ARG_OK(p != nullptr && bytes > 0, "bad arguments");
+    *p = nullptr;
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    ORB_CUDA_OK(cudaMalloc(p, bytes));
+    return ORBB200_OK;
+}
+int orbb200_device_free(void *p)
+{
+    if (p) ORB_CUDA_OK(cudaFree(p));
+    return ORBB200_OK;
+}
+int orbb200_copy_to_device(void *dst_d, const void *src, size_t bytes)
+{
+    if (bytes == 0) return ORBB200_OK;
+    ORB_ARG_OK(dst_d && src, "null pointer");
+    ORB_CUDA_OK(cudaMemcpy(dst_d, src, bytes, cudaMemcpyHostToDevice));
+    count_h2d(bytes);
+    return ORBB200_OK;
+}
+int orbb200_copy_to_host(void *dst, const void *src_d, size_t bytes)
+{
+    if (bytes == 0) return ORBB200_OK;
+    ORB_ARG_OK(dst && src_d, "null pointer");
+    ORB_CUDA_OK(cudaMemcpy(dst, src_d, bytes, cudaMemcpyDeviceToHost));
+    return ORBB200_OK;
+}
+int orbb200_copy_on_device(void *dst_d, const void *src_d, size_t bytes)
+{
+    if (bytes == 0) return ORBB200_OK;
+    ORB_ARG_OK(dst_d && src_d, "null pointer");
+    ORB_CUDA_OK(cudaMemcpy(dst_d, src_d, bytes, cudaMemcpyDeviceToDevice));
+    return ORBB200_OK;
+}
+unsigned long long orbb200_h2d_bytes_total(void) { return g_h2dBytes.load(); }
+int orbb200_device_sync(int device)
+{
+    int rc = scratch_bind(device);
+    if (rc) return rc;
+    ORB_CUDA_OK(cudaDeviceSynchronize());
     return ORBB200_OK;
 }
 

@@ -92,6 +92,18 @@ def test_facade_matcher_templates_equal_reference_loops():
     assert r.returncode == 0 and r.stdout.count("ok ") == 16 and "FAIL" not in r.stdout, r.stdout + r.stderr
 
 
+def test_device_resident_frame_searches_without_reupload(tmp_path):
+    """orbb200::DeviceFrame (SURVEY 8f rank 1): Adopt after operator(), device undistortion, lazy host views, and the facade's
+    windowed search on the resident frame == the host-frame search, with the H2D byte counter moving by the queries only"""
+    exe = os.path.join(ROOT, "orb-slam2_b200", "facade_device_frame.bin")
+    assert os.path.exists(exe), "facade_device_frame.bin not built: run __graft_entry__.build()"
+    img = synth.textured_frame(640, 480, 1000)
+    p = str(tmp_path / "img.raw")
+    img.tofile(p)
+    r = subprocess.run([exe, "640", "480", p], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.count("ok ") == 5 and "FAIL" not in r.stdout, r.stdout + r.stderr
+
+
 def test_facade_matcher_equals_compiled_reference_on_reference_types():
     """All twelve searches of include/orbb200/ORBmatcher.h, bound to the REFERENCE's own Frame / KeyFrame / MapPoint / Map
     classes, against the REFERENCE's own ORBmatcher.cc (oracle/_ref/liborbslam_ref.so = the unmodified sources compiled by
