@@ -193,6 +193,17 @@ int orbb200_match_bruteforce_top2(const uint8_t *q, int nq, const uint8_t *db, i
                                   int device);
 int orbb200_match_bruteforce_top2_device(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb,
                                          orbb200_top2 *out_d, int index_offset, void *stream);
+/* NO counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same search, same kernels, same result as
+ * orbb200_match_bruteforce_top2_device on the CURRENT device, but it allocates nothing: the per-chunk partial results live in a
+ * static 8 MiB device array that every GPU loading the library holds until exit.  Limit: (database chunks) x nq <= 524 288 partial
+ * records of 16 bytes.  The launch plan uses at most floor(592 / ceil(nq / 512)) chunks, i.e. at most 303 104 records while the
+ * database is chunked (BASELINE config 5, 2048 x 1 048 576: 148 chunks, 303 104 records) and nq records once it is not: the limit
+ * is nq <= 524 288 queries per call, any database size.  Beyond it the call returns ORBB200_ERR_CAPACITY and launches nothing.
+ * stream == NULL is the default stream (no stream is created).  All calls on a device share the array, which keeps the last call's
+ * contents (nothing needs clearing: every record a call reads it has written first); calls that OVERLAP on the GPU race on it. */
+int orbb200_match_bruteforce_top2_device_noalloc(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb,
+                                                 orbb200_top2 *out_d, int index_offset, void *stream);
 
 /* M2-M9 core: per-query candidate lists (CSR: cand_offsets[nq+1], cand_idx) visited in list order -- the
  * inner loops of SearchByProjection (src/ORBmatcher.cc:90-123, 1482-1508), SearchByBoW (:214-240),

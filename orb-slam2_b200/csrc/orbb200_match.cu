@@ -95,6 +95,32 @@ static int bf_launch(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, o
     return ORBB200_OK;
 }
 
+// ---- orbb200_match_bruteforce_top2_device_noalloc: the per-chunk partial results live in a static device array --------------------
+// Every GPU that loads the library holds these 8 MiB until exit.  All calls on a device share the array.
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)8 << 20;
+constexpr size_t NOALLOC_MAX_PARTIALS = NOALLOC_SCRATCH_BYTES / sizeof(orbb200_top2); // 524 288 (chunk, query) records
+static __device__ __align__(256) unsigned char g_noallocScratch[NOALLOC_SCRATCH_BYTES];
+static std::mutex g_noallocMu;
+static void *g_noallocPtr[64] = {};
+
+// device address of g_noallocScratch on the CURRENT device: in host code the array's name is only a stand-in for the symbol, so
+// the address is asked for once per device, with that device current, and cached
+static int noalloc_scratch_ptr(orbb200_top2 **out)
+{
+    int device = -1;
+    ORB_CUDA_OK(cudaGetDevice(&device));
+    ORB_ARG_OK(device >= 0 && device < 64, "device ordinal out of range");
+    std::lock_guard<std::mutex> lk(g_noallocMu);
+    if (!g_noallocPtr[device]) {
+        void *p = nullptr;
+        ORB_CUDA_OK(cudaGetSymbolAddress(&p, g_noallocScratch));
+        ORB_ARG_OK(p != nullptr && ((size_t)p & 255) == 0, "cudaGetSymbolAddress returned an unusable address");
+        g_noallocPtr[device] = p;
+    }
+    *out = (orbb200_top2 *)g_noallocPtr[device];
+    return ORBB200_OK;
+}
+
 } // namespace orbb200
 
 // config 5 on N GPUs: one exchange region per rank (gather slots + flags), mapped into every peer with CUDA IPC
@@ -142,6 +168,35 @@ int orbb200_match_bruteforce_top2_device(const uint8_t *q_d, int nq, const uint8
     int rc = scratch_bind(-1);
     if (rc) return rc;
     return bf_launch(q_d, nq, db_d, ndb, out_d, index_offset, stream ? (cudaStream_t)stream : g_scratch.stream);
+}
+
+// No counterpart in the reference; added for callers that cannot allocate (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  Same kernels and the same result as orbb200_match_bruteforce_top2_device; the
+// per-chunk partial top-2 records go to the static device array above instead of a cudaMalloc'ed scratch buffer.  Nothing here
+// allocates: no cudaMalloc / cudaFree, no stream or event creation (stream == NULL is the default stream of the current device).
+// The array keeps the last call's contents; nothing in it has to start at zero because k_bf_top2 writes every (chunk, query) record
+// that k_merge_top2 of the same call reads.  Calls that overlap on the GPU (different streams, different host threads) race on it.
+int orbb200_match_bruteforce_top2_device_noalloc(const uint8_t *q_d, int nq, const uint8_t *db_d, int ndb, orbb200_top2 *out_d,
+                                                 int index_offset, void *stream)
+{
+    ORB_ARG_OK(q_d && db_d && out_d && nq > 0 && ndb > 0, "bad arguments");
+    ORB_ARG_OK(((size_t)q_d & 15) == 0 && ((size_t)db_d & 15) == 0, "descriptor arrays must be 16-byte aligned");
+    int groups, chunks, rows;
+    bf_plan(nq, ndb, &groups, &chunks, &rows);
+    if ((size_t)chunks * (size_t)nq > NOALLOC_MAX_PARTIALS) {
+        set_error("orbb200_match_bruteforce_top2_device_noalloc: %d queries x %d database chunks = %zu partial records exceed the static "
+                  "scratch of %zu records (%zu bytes); use orbb200_match_bruteforce_top2_device or split the queries",
+                  nq, chunks, (size_t)chunks * (size_t)nq, NOALLOC_MAX_PARTIALS, NOALLOC_SCRATCH_BYTES);
+        return ORBB200_ERR_CAPACITY;
+    }
+    orbb200_top2 *partial = nullptr;
+    int rc = noalloc_scratch_ptr(&partial);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    k_bf_top2<false><<<dim3(groups, chunks), BF_THREADS, 0, st>>>(q_d, nq, db_d, ndb, rows, index_offset, partial, ExchangeParams());
+    k_merge_top2<<<div_up(nq * 32, 256), 256, 0, st>>>(partial, chunks, nq, out_d);
+    ORB_CUDA_OK(cudaGetLastError());
+    return ORBB200_OK;
 }
 
 int orbb200_match_bruteforce_top2(const uint8_t *q, int nq, const uint8_t *db, int ndb, orbb200_top2 *out, int device)

@@ -22,7 +22,7 @@ EXPORTS = [
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
     "orbb200_debug_blurred_level", "orbb200_descriptor_distance", "orbb200_match_bruteforce_top2",
-    "orbb200_match_bruteforce_top2_device", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_search_triangulation", "orbb200_window_search", "orbb200_merge_top2",
+    "orbb200_match_bruteforce_top2_device", "orbb200_match_bruteforce_top2_device_noalloc", "orbb200_match_candidates", "orbb200_candidate_distances", "orbb200_search_triangulation", "orbb200_window_search", "orbb200_merge_top2",
     "orbb200_merge_top2_device", "orbb200_stereo_match", "orbb200_stereo_match_batch",
     "orbb200_stereo_match_batch_device", "orbb200_extract_stereo_batch", "orbb200_popc_peak", "orbb200_last_error", "orbb200_version",
     "orbb200_vocabulary_load_text", "orbb200_vocabulary_create", "orbb200_vocabulary_destroy", "orbb200_vocabulary_info",
@@ -80,6 +80,7 @@ def lib():
     L.orbb200_descriptor_distance.argtypes = [vp, vp, ip, vp, ip]
     L.orbb200_match_bruteforce_top2.argtypes = [vp, ip, vp, ip, vp, ip]
     L.orbb200_match_bruteforce_top2_device.argtypes = [vp, ip, vp, ip, vp, ip, vp]
+    L.orbb200_match_bruteforce_top2_device_noalloc.argtypes = [vp, ip, vp, ip, vp, ip, vp]
     L.orbb200_match_candidates.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
     L.orbb200_candidate_distances.argtypes = [vp, ip, vp, ip, vp, vp, vp, ip]
     L.orbb200_search_triangulation.argtypes = [vp, vp, vp, ip, vp, vp, vp, ip, vp, vp, vp, fp, fp, vp, vp, ip, ip, vp, vp, ip]
