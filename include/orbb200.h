@@ -126,6 +126,12 @@ int orbb200_bind_host_to_device(int device);
 int orbb200_host_alloc(void **p, size_t bytes);
 int orbb200_host_free(void *p);
 
+/* Tuning / test knob of the quadtree stage (DistributeOctTree, src/ORBextractor.cc:617-915): the kernel builds the tree from a
+ * histogram of the keys down to a fixed depth (7 by default, less when shared memory is short) and falls back to an iterative
+ * formulation without depth limit when a node has to be split below it.  max_depth caps that depth; 0 = iterative formulation only.
+ * The result is the same for every value (tests/test_gpu_extract.py runs 0, 2 and the default against the oracle). */
+int orbb200_extractor_set_octree_depth(orbb200_extractor *e, int max_depth);
+
 /* single-image calls (orbb200_extract / orbb200_extract_color) replay a CUDA graph captured per (shape, capacity): pinned bounce
  * buffers, one graph launch, one synchronisation.  on = 0 sends them through the batch pipeline instead (A/B measurements). */
 int orbb200_extractor_set_graph(orbb200_extractor *e, int on);

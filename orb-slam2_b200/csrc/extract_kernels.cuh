@@ -24,6 +24,7 @@ struct LevelGeom {
     int nfeat, nIni;
     float hX;
     int nodeCap, nodeOff, sortLen;
+    int octDepth;             // depth of the quadtree kernel's histogram (0: iterative formulation only), octree_kernel.cuh
     unsigned int nodeWsOff;
     float scale, patch;
     int blurTileBase, blurTilesX, blurTilesY;
@@ -47,6 +48,7 @@ struct ExtractParams {
     int totalCells;
     int *nodeWs;
     size_t nodeWsStride;
+    int octDepthCap;          // orbb200_extractor_set_octree_depth: caps LevelGeom::octDepth (tests force the fallback with it)
     uint32_t *lvlKp;
     int nodeTotal;
     int *lvlCount;

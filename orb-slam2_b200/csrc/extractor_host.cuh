@@ -20,6 +20,7 @@ struct orbb200_extractor {
     size_t pyrStride = 0, candStride = 0, nodeWsStride = 0;
     int totalCells = 0, nodeTotal = 0, totalBlurTiles = 0, coefTotal = 0;
     size_t octreeSmem = 0;
+    int octDepthCap = 7; // OCT_MAX_DEPTH
     int fastRows = 7; // staged ROI rows of the tallest cell row (k_fast_strips dynamic shared memory)
     int totalStrips = 0;
     // device buffers

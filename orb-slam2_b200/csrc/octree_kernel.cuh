@@ -51,6 +51,339 @@ __device__ __forceinline__ int key_quadrant(uint32_t k, int xs, int ys)
     return (x < xs ? 0 : 1) + (y < ys ? 0 : 2);
 }
 
+// =====================================================================================================================
+// Fast path: the tree is built from a HISTOGRAM of the keys, the keys themselves are read twice.
+//
+// DivideNode's split points depend on the node's bounds only (x0 + ceil((x1 - x0) / 2), :553-554), never on its keys, so the
+// path of a key through the tree -- root, then one x-bit and one y-bit per depth -- is a function of its coordinates: two small
+// tables (x -> root and D x-bits, y -> D y-bits) built per block.  One pass over the keys counts them in the 2^D x 2^D deepest
+// cells of their root (16-bit shared-memory counters), a pyramid of sums gives the key count of every possible node at every
+// depth, and the reference's passes (:733-884) then run on the NODE LIST alone: "how many keys does child q get" is a table
+// lookup instead of a pass over the keys, and no key ever has to be told which node it moved to.  When the list is final, every
+// deepest cell is painted with the list position of the node that covers it and a second pass over the keys takes, per node,
+// the maximum response with the reference's first-in-list-order tie-break (:895-912): the order key is the key's position in the
+// cell-major candidate array (cell-row-major, row-major inside a cell = the order the reference appends them in, :925-1009).
+// A node that must be split below depth D (keys clustered in one deepest cell) makes the block fall back to the iterative
+// formulation below, which has no depth limit.  4K level 0 (328 k keys): 12 passes over the keys -> 2.
+constexpr int OCT_MAX_DEPTH = 7;
+
+__host__ __device__ inline size_t oct_fast_up_total(int nIni, int D) { return (size_t)nIni * (size_t)(((1 << (2 * D)) - 1) / 3); }
+// shared memory of the fast path: pyramid levels 0..D-1 (int), deepest level (u16), 10 node arrays of C ints, sort keys, x / y tables
+__host__ __device__ inline size_t oct_fast_smem(int nIni, int D, int C, int sortLen, int width, int height)
+{
+    size_t b = 4 * oct_fast_up_total(nIni, D) + 2 * ((size_t)nIni << (2 * D)) + 4 * (size_t)10 * C;
+    b = (b + 7) & ~(size_t)7;
+    b += 8 * (size_t)sortLen + 2 * (size_t)((width + 1) & ~1) + (size_t)height;
+    return (b + 15) & ~(size_t)15;
+}
+
+struct OctCtl { int size, finish, mode, seq, nexp, rstar, ovf; };
+
+__device__ __forceinline__ int oct_pack(int r, int d, int xp, int yp) { return xp | (yp << 8) | (d << 16) | (r << 20); }
+
+// key count of the node (root r, depth d, x prefix xp, y prefix yp)
+__device__ __forceinline__ int oct_count(const int *up, const unsigned short *deep, int nIni, int D, int r, int d, int xp, int yp)
+{
+    const int i = (r << (2 * d)) + (yp << d) + xp;
+    return d == D ? (int)deep[i] : up[nIni * (((1 << (2 * d)) - 1) / 3) + i];
+}
+
+// f(key, pos) for every candidate of the level; pos = its position in the cell-major candidate array (ascends in the reference's
+// order).  A warp takes 32 consecutive cells, scans their counts and walks the concatenated keys with all lanes busy, OCT_FKU
+// independent loads per lane in flight.
+constexpr int OCT_FKU = 4;
+template <class F> __device__ __forceinline__ void oct_for_each_key(const uint32_t *cand, const int *cellCount, int nCells, int cellCap, F f)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int c0 = wid * 32; c0 < nCells; c0 += nw * 32) {
+        const int cnt = c0 + lane < nCells ? min(cellCount[c0 + lane], cellCap) : 0;
+        int inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        const int excl = inc - cnt, T = __shfl_sync(0xffffffffu, inc, 31);
+        for (int t0 = 0; t0 < T; t0 += 32 * OCT_FKU) {
+            uint32_t key[OCT_FKU];
+            int pos[OCT_FKU];
+#pragma unroll
+            for (int u = 0; u < OCT_FKU; u++) {
+                const int t = t0 + u * 32 + lane;
+                int j = 0; // number of cells whose inclusive count is <= t = the cell that holds key t
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int v = __shfl_sync(0xffffffffu, inc, j + step - 1);
+                    if (v <= t) j += step;
+                }
+                const int e = __shfl_sync(0xffffffffu, excl, j & 31);
+                pos[u] = -1;
+                key[u] = 0u;
+                if (t < T) {
+                    pos[u] = (c0 + j) * cellCap + (t - e);
+                    key[u] = __ldg(cand + pos[u]);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < OCT_FKU; u++)
+                if (pos[u] >= 0) f(key[u], pos[u]);
+        }
+    }
+}
+
+// returns false (block-uniform) when a node at the depth limit has to be split; nothing has been written then
+template <int MAXT> __device__ bool octree_fast(const ExtractParams &P, const LevelGeom &g, int l, int b, int D, unsigned char *dsm,
+                                                int *scanTmp, OctCtl *ctl)
+{
+    const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = NT >> 5;
+    const int C = g.nodeCap, N = g.nfeat, nIni = g.nIni;
+    const int width = max(g.w - 32, 1), height = max(g.h - 32, 1);
+    const int S2 = 1 << (2 * D);
+    int *up = reinterpret_cast<int *>(dsm);
+    const int upTotal = (int)oct_fast_up_total(nIni, D);
+    unsigned short *deep = reinterpret_cast<unsigned short *>(up + upTotal);
+    int *nodeBase = reinterpret_cast<int *>(deep + (size_t)nIni * S2);
+    int *curCode = nodeBase, *curCnt = nodeBase + C, *curSeq = nodeBase + 2 * C;
+    int *nxtCode = nodeBase + 3 * C, *nxtCnt = nodeBase + 4 * C, *nxtSeq = nodeBase + 5 * C;
+    int *vrank = nodeBase + 6 * C, *vis = nodeBase + 7 * C, *basea = nodeBase + 8 * C, *cum = nodeBase + 9 * C;
+    size_t off = 4 * (size_t)upTotal + 2 * (size_t)nIni * S2 + 4 * (size_t)10 * C;
+    off = (off + 7) & ~(size_t)7;
+    unsigned long long *skeys = reinterpret_cast<unsigned long long *>(dsm + off);
+    unsigned short *xtab = reinterpret_cast<unsigned short *>(skeys + g.sortLen);
+    unsigned char *ytab = reinterpret_cast<unsigned char *>(xtab + ((width + 1) & ~1));
+    const int *cellCount = P.cellCount + (size_t)b * P.totalCells + g.cellBase;
+    const uint32_t *cand = P.cand + (size_t)b * P.candStride + g.candOff;
+
+    // ---- coordinate tables: root (:627-704) and the D split decisions along each axis (DivideNode :551-609)
+    for (int x = tid; x < width; x += NT) {
+        int r = (int)__fdiv_rn((float)x, g.hX);
+        r = min(r, nIni - 1);
+        int x0 = (int)__fmul_rn(g.hX, (float)r), x1 = (int)__fmul_rn(g.hX, (float)(r + 1)), xb = 0;
+        for (int d = 0; d < D; d++) {
+            const int xs = x0 + ((x1 - x0 + 1) >> 1);
+            const int bit = x < xs ? 0 : 1;
+            if (bit) x0 = xs; else x1 = xs;
+            xb = 2 * xb + bit;
+        }
+        xtab[x] = (unsigned short)(xb | (r << 8));
+    }
+    for (int y = tid; y < height; y += NT) {
+        int y0 = 0, y1 = g.h - 32, yb = 0;
+        for (int d = 0; d < D; d++) {
+            const int ys = y0 + ((y1 - y0 + 1) >> 1);
+            const int bit = y < ys ? 0 : 1;
+            if (bit) y0 = ys; else y1 = ys;
+            yb = 2 * yb + bit;
+        }
+        ytab[y] = (unsigned char)yb;
+    }
+    {
+        unsigned int *z = reinterpret_cast<unsigned int *>(deep);
+        for (int i = tid; i < (nIni * S2) >> 1; i += NT) z[i] = 0u;
+    }
+    __syncthreads();
+    // ---- pass 1 over the keys: deepest-cell histogram (two 16-bit counters per word; a cell holds far fewer than 65 536 pixels)
+    {
+        unsigned int *h = reinterpret_cast<unsigned int *>(deep);
+        oct_for_each_key(cand, cellCount, g.nCells, g.cellCap, [&](uint32_t key, int) {
+            const int xt = xtab[min((int)(key & 0xFFF), width - 1)], yb = ytab[min((int)((key >> 12) & 0xFFF), height - 1)];
+            const int idx = ((xt >> 8) << (2 * D)) + (yb << D) + (xt & 0xFF);
+            atomicAdd(h + (idx >> 1), 1u << (16 * (idx & 1)));
+        });
+    }
+    __syncthreads();
+    // ---- pyramid of sums: level d cell (r, yp, xp) = its four children at level d + 1
+    for (int d = D - 1; d >= 0; d--) {
+        int *dst = up + nIni * (((1 << (2 * d)) - 1) / 3);
+        const int cells = nIni << (2 * d), m = (1 << d) - 1;
+        for (int i = tid; i < cells; i += NT) {
+            const int r = i >> (2 * d), yp = (i >> d) & m, xp = i & m;
+            dst[i] = oct_count(up, deep, nIni, D, r, d + 1, 2 * xp, 2 * yp) + oct_count(up, deep, nIni, D, r, d + 1, 2 * xp + 1, 2 * yp) +
+                     oct_count(up, deep, nIni, D, r, d + 1, 2 * xp, 2 * yp + 1) + oct_count(up, deep, nIni, D, r, d + 1, 2 * xp + 1, 2 * yp + 1);
+        }
+        __syncthreads();
+    }
+    // ---- roots
+    if (tid == 0) {
+        int pos = 0;
+        for (int r = 0; r < nIni; r++) {
+            const int c = up[r];
+            if (c > 0) { curCode[pos] = oct_pack(r, 0, 0, 0); curCnt[pos] = c; curSeq[pos] = r; pos++; }
+        }
+        ctl->size = pos; ctl->finish = 0; ctl->mode = 0; ctl->seq = nIni; ctl->ovf = 0x7fffffff;
+    }
+
+    // ---- the reference's passes on the node list
+    int *cur[3] = {curCode, curCnt, curSeq}, *nxt[3] = {nxtCode, nxtCnt, nxtSeq};
+    while (true) {
+        __syncthreads();
+        if (ctl->finish) break;
+        const int size = ctl->size, mode = ctl->mode, seq0 = ctl->seq;
+        const int *cCode = cur[0], *cCnt = cur[1], *cSeq = cur[2];
+        int *nCode = nxt[0], *nCnt = nxt[1], *nSeq = nxt[2];
+        int nvis = 0;
+        // (1) visit list: mode 0 (:733-799) every node with more than one key in list order; mode 1 (:814-884) those nodes sorted
+        //     by (nKeys, creation sequence), largest first
+        if (mode == 0) {
+            for (int base = 0; base < size; base += NT) {
+                const int p = base + tid;
+                const int f = (p < size && cCnt[p] > 1) ? 1 : 0;
+                int tot;
+                const int ex = block_excl_scan(f, scanTmp, &tot);
+                if (p < size) vrank[p] = f ? nvis + ex : -1;
+                if (f) vis[nvis + ex] = p;
+                nvis += tot;
+            }
+        } else {
+            for (int base = 0; base < size; base += NT) {
+                const int p = base + tid;
+                const int f = (p < size && cCnt[p] > 1) ? 1 : 0;
+                int tot;
+                const int ex = block_excl_scan(f, scanTmp, &tot);
+                if (p < size) vrank[p] = -1;
+                if (f)
+                    skeys[nvis + ex] = ((unsigned long long)cCnt[p] << 40) | ((unsigned long long)(cSeq[p] & 0xFFFFF) << 20) | (unsigned long long)p;
+                nvis += tot;
+            }
+            int S = 1;
+            while (S < nvis) S <<= 1;
+            for (int i = nvis + tid; i < S; i += NT) skeys[i] = 0ull;
+            __syncthreads();
+            for (int k = 2; k <= S; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < S; i += NT) {
+                        const int ixj = i ^ j;
+                        if (ixj > i) {
+                            const unsigned long long a = skeys[i], c = skeys[ixj];
+                            const bool desc = (i & k) == 0;
+                            if (desc ? a < c : a > c) { skeys[i] = c; skeys[ixj] = a; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            for (int r = tid; r < nvis; r += NT) {
+                const int p = (int)(skeys[r] & 0xFFFFFull);
+                vis[r] = p;
+                vrank[p] = r;
+            }
+        }
+        if (tid == 0) { ctl->nexp = 0; ctl->rstar = nvis - 1; ctl->ovf = 0x7fffffff; }
+        __syncthreads();
+        // (3) creation index of the children (non-empty quadrants, :567-609); a visited node at the depth limit has no child table
+        int T = 0;
+        for (int base = 0; base < nvis; base += NT) {
+            const int r = base + tid;
+            int nch = 0;
+            if (r < nvis) {
+                const int code = cCode[vis[r]];
+                const int d = (code >> 16) & 15, xp = code & 255, yp = (code >> 8) & 255, rt = code >> 20;
+                if (d >= D) atomicMin(&ctl->ovf, r);
+                else
+                    nch = (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp, 2 * yp) > 0) + (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp + 1, 2 * yp) > 0) +
+                          (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp, 2 * yp + 1) > 0) + (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp + 1, 2 * yp + 1) > 0);
+            }
+            int tot;
+            const int ex = block_excl_scan(nch, scanTmp, &tot);
+            if (r < nvis) {
+                basea[r] = T + ex;
+                cum[r] = T + ex + nch - (r + 1); // list growth after splitting visit ranks 0..r
+            }
+            T += tot;
+        }
+        int nsplit = nvis;
+        if (mode == 1) {
+            for (int r = tid; r < nvis; r += NT)
+                if (size + cum[r] >= N) atomicMin(&ctl->rstar, r);
+            __syncthreads();
+            nsplit = ctl->rstar + 1;
+        }
+        __syncthreads();
+        if (ctl->ovf < nsplit) return false; // ranks below the first depth-limited node were exact, so this decision is too
+        if (mode == 1) {
+            for (int r = nsplit + tid; r < nvis; r += NT) vrank[vis[r]] = -1;
+            T = 0;
+            if (nsplit > 0) {
+                const int code = cCode[vis[nsplit - 1]];
+                const int d = (code >> 16) & 15, xp = code & 255, yp = (code >> 8) & 255, rt = code >> 20;
+                T = basea[nsplit - 1] + (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp, 2 * yp) > 0) + (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp + 1, 2 * yp) > 0) +
+                    (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp, 2 * yp + 1) > 0) + (oct_count(up, deep, nIni, D, rt, d + 1, 2 * xp + 1, 2 * yp + 1) > 0);
+            }
+            __syncthreads();
+        }
+        // (4) children at the front in reverse creation order (push_front, :748...) ...
+        int nexp = 0;
+        for (int r = tid; r < nsplit; r += NT) {
+            const int code = cCode[vis[r]];
+            const int d = (code >> 16) & 15, xp = code & 255, yp = (code >> 8) & 255, rt = code >> 20;
+            int ci = basea[r];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int cx = 2 * xp + (q & 1), cy = 2 * yp + (q >> 1);
+                const int c = oct_count(up, deep, nIni, D, rt, d + 1, cx, cy);
+                if (c > 0) {
+                    const int np = T - 1 - ci;
+                    nCode[np] = oct_pack(rt, d + 1, cx, cy);
+                    nCnt[np] = c;
+                    nSeq[np] = seq0 + ci;
+                    nexp += c > 1;
+                    ci++;
+                }
+            }
+        }
+        if (nexp) atomicAdd(&ctl->nexp, nexp);
+        // ... then the unsplit nodes in their old order
+        int nsurv = 0;
+        for (int base = 0; base < size; base += NT) {
+            const int p = base + tid;
+            const int f = (p < size && vrank[p] < 0) ? 1 : 0;
+            int tot;
+            const int ex = block_excl_scan(f, scanTmp, &tot);
+            if (f) {
+                const int np = T + nsurv + ex;
+                nCode[np] = cCode[p]; nCnt[np] = cCnt[p]; nSeq[np] = cSeq[p];
+            }
+            nsurv += tot;
+        }
+        __syncthreads();
+        const int newSize = T + nsurv;
+        if (tid == 0) {
+            ctl->size = newSize;
+            ctl->seq = seq0 + T;
+            if (newSize >= N || newSize == size) ctl->finish = 1;
+            else if (mode == 0 && newSize + ctl->nexp * 3 > N) ctl->mode = 1;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) { int *t = cur[k]; cur[k] = nxt[k]; nxt[k] = t; }
+    }
+    // ---- paint every deepest cell with the list position of the final node that covers it
+    const int size = ctl->size;
+    const int *fCode = cur[0];
+    for (int p = wid; p < size; p += nw) {
+        const int code = fCode[p];
+        const int d = (code >> 16) & 15, xp = code & 255, yp = (code >> 8) & 255, rt = code >> 20;
+        const int sh = D - d, side = 1 << sh;
+        unsigned short *base = deep + ((size_t)rt << (2 * D)) + ((size_t)(yp << sh) << D) + (xp << sh);
+        for (int i = lane; i < side * side; i += 32) base[((i >> sh) << D) + (i & (side - 1))] = (unsigned short)p;
+    }
+    unsigned int *best = reinterpret_cast<unsigned int *>(vrank);
+    for (int p = tid; p < size; p += NT) best[p] = 0u;
+    __syncthreads();
+    // ---- pass 2 over the keys: one keypoint per node, maximum response, first in the reference's order on ties (:895-912)
+    oct_for_each_key(cand, cellCount, g.nCells, g.cellCap, [&](uint32_t key, int pos) {
+        const int xt = xtab[min((int)(key & 0xFFF), width - 1)], yb = ytab[min((int)((key >> 12) & 0xFFF), height - 1)];
+        const int node = deep[((xt >> 8) << (2 * D)) + (yb << D) + (xt & 0xFF)];
+        atomicMax(best + node, ((key >> 24) << 24) | (0xFFFFFFu - (unsigned int)pos));
+    });
+    __syncthreads();
+    uint32_t *out = P.lvlKp + (size_t)b * P.nodeTotal + g.nodeOff;
+    for (int p = tid; p < size; p += NT) out[p] = cand[0xFFFFFFu - (best[p] & 0xFFFFFFu)];
+    if (tid == 0) P.lvlCount[(size_t)b * P.nlevels + l] = size;
+    return true;
+}
+
+// =====================================================================================================================
+// Iterative formulation (no depth limit): the fallback of the fast path, and the only path when the fast path's tables do not
+// fit in shared memory (extreme aspect ratios: many roots).
 // workspace (ints) per (image, level): 2 node buffers (6C each) + vrank C + vis C + base C + cum C (21C reserved);
 // shared memory: everything the two per-key loops of a pass touch per node -- quadrant counts cc 4C, child positions
 // 4C, new positions C, split coordinates recX / recY C each (recX < 0: node not split in this pass) -- + sort keys
@@ -77,6 +410,14 @@ template <int MAXT, int MINB> __global__ void __launch_bounds__(MAXT, MINB) k_oc
     NodeBuf cur = node_buf(ws, C), nxt = node_buf(ws + 6 * C, C);
     int *vrank = ws + 16 * C, *vis = ws + 18 * C, *basea = ws + 19 * C, *cum = ws + 20 * C;
 
+    {
+        __shared__ OctCtl fctl;
+        const int D = min(g.octDepth, P.octDepthCap);
+        if (D > 0) {
+            if (octree_fast<MAXT>(P, g, l, b, D, dsm, scanTmp, &fctl)) return;
+            __syncthreads();
+        }
+    }
     // ---- gather the cells' candidates in the reference's order (cell-row-major, row-major inside a cell)
     int n = 0;
     for (int base = 0; base < g.nCells; base += NT) {

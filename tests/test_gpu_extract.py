@@ -239,3 +239,32 @@ def test_single_image_graph_path_equals_batch_pipeline(configs):
     ks, ds = ex(big[:, :640])
     kr, dr = ref_cpu.RefExtractor(1000, 1.2, 8, 20, 7).extract(img)
     _compare(ks, ds, kr, dr)
+
+
+@pytest.mark.parametrize("name", ["tum", "kitti"])
+def test_quadtree_formulations_agree(configs, name):
+    """DistributeOctTree on the device (src/ORBextractor.cc:617-915): the histogram formulation (default depth), the histogram
+    formulation forced to overflow its depth (2, 3: blocks fall back mid-way) and the iterative formulation alone (0) must give the
+    oracle's keypoints -- also on a clustered image (texture in one corner only: deep, unbalanced tree) and in a batch."""
+    w, h, nf, sfac, nl, ini, mn = configs[name]
+    img = synth.textured_frame(w, h, 77)
+    clustered = np.full_like(img, 128)
+    clustered[h // 2:h // 2 + h // 5, w // 3:w // 3 + w // 6] = img[h // 2:h // 2 + h // 5, w // 3:w // 3 + w // 6]
+    clustered[20:60, 20:90] = img[20:60, 20:90]
+    ref = ref_cpu.RefExtractor(nf, sfac, nl, ini, mn)
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    for im in (img, clustered):
+        kc, dc = ref.extract(im)
+        assert len(kc) > 50
+        for depth in (7, 0, 2, 3, 7):
+            ex.set_octree_depth(depth)
+            for graph in (1, 0):
+                ex.set_graph(graph)
+                kg, dg = ex(im)
+                _compare(kg, dg, kc, dc)
+    ex.set_octree_depth(7)
+    batch = np.stack([img, clustered, img])
+    kps, desc, n = ex.extract_batch(batch)
+    for b, im in enumerate((img, clustered, img)):
+        kc, dc = ref.extract(im)
+        _compare(kps[b, :n[b]], desc[b, :n[b]], kc, dc)
