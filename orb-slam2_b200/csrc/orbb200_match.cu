@@ -24,6 +24,10 @@ struct Scratch {
     // different caller streams: the event orders each search behind the previous user of the buffer
     cudaEvent_t partialDone = nullptr;
     bool partialUsed = false;
+    // frame-sized searches: all inputs of a call travel in ONE copy from a pinned staging block, all outputs come back in one
+    // (or are written by the kernel straight into the mapped pinned block), so a call costs one synchronisation
+    unsigned char *hIn = nullptr, *dIn = nullptr, *hOut = nullptr, *dOut = nullptr, *hOutDev = nullptr;
+    size_t hInCap = 0, dInCap = 0, hOutCap = 0, dOutCap = 0;
 };
 static thread_local Scratch g_scratch;
 
@@ -42,6 +46,8 @@ static int scratch_bind(int device)
         s.stream = nullptr;
         s.partialDone = nullptr;
         s.partialUsed = false;
+        s.hIn = s.dIn = s.hOut = s.dOut = s.hOutDev = nullptr;
+        s.hInCap = s.dInCap = s.hOutCap = s.dOutCap = 0;
         s.device = device;
     }
     if (!s.stream) ORB_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
@@ -60,6 +66,69 @@ static int scratch_get(int slot, size_t bytes, void **out)
     *out = s.buf[slot];
     return ORBB200_OK;
 }
+
+static inline size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+// Packed transfers of the frame-sized searches.  Usage: sizes first (in(bytes) / out(bytes) return offsets), reserve(), then
+// put() the inputs, upload(), launch on dIn + offset / dOut + offset, download(), synchronise, read hOut + offset.
+struct Pack {
+    size_t inBytes = 0, outBytes = 0;
+    size_t in(size_t bytes) { const size_t o = inBytes; inBytes += pad256(bytes); return o; }
+    size_t out(size_t bytes) { const size_t o = outBytes; outBytes += pad256(bytes); return o; }
+    int reserve()
+    {
+        Scratch &s = g_scratch;
+        if (s.hInCap < inBytes || s.dInCap < inBytes || s.hOutCap < outBytes || s.dOutCap < outBytes) ORB_CUDA_OK(cudaStreamSynchronize(s.stream));
+        if (s.hInCap < inBytes) {
+            if (s.hIn) cudaFreeHost(s.hIn);
+            s.hIn = nullptr; s.hInCap = 0;
+            const size_t nb = std::max<size_t>(pad256(inBytes + inBytes / 2), 1 << 16);
+            ORB_CUDA_OK(cudaHostAlloc((void **)&s.hIn, nb, cudaHostAllocDefault));
+            s.hInCap = nb;
+        }
+        if (s.dInCap < inBytes) {
+            if (s.dIn) cudaFree(s.dIn);
+            s.dIn = nullptr; s.dInCap = 0;
+            const size_t nb = std::max<size_t>(pad256(inBytes + inBytes / 2), 1 << 16);
+            ORB_CUDA_OK(cudaMalloc((void **)&s.dIn, nb));
+            s.dInCap = nb;
+        }
+        if (s.hOutCap < outBytes) {
+            if (s.hOut) cudaFreeHost(s.hOut);
+            s.hOut = nullptr; s.hOutCap = 0; s.hOutDev = nullptr;
+            const size_t nb = std::max<size_t>(pad256(outBytes + outBytes / 2), 1 << 16);
+            ORB_CUDA_OK(cudaHostAlloc((void **)&s.hOut, nb, cudaHostAllocMapped));
+            ORB_CUDA_OK(cudaHostGetDevicePointer((void **)&s.hOutDev, s.hOut, 0));
+            s.hOutCap = nb;
+        }
+        if (s.dOutCap < outBytes) {
+            if (s.dOut) cudaFree(s.dOut);
+            s.dOut = nullptr; s.dOutCap = 0;
+            const size_t nb = std::max<size_t>(pad256(outBytes + outBytes / 2), 1 << 16);
+            ORB_CUDA_OK(cudaMalloc((void **)&s.dOut, nb));
+            s.dOutCap = nb;
+        }
+        return ORBB200_OK;
+    }
+    template <class T> const T *put(size_t off, const void *src, size_t bytes) const
+    {
+        if (bytes) memcpy(g_scratch.hIn + off, src, bytes);
+        return reinterpret_cast<const T *>(g_scratch.dIn + off);
+    }
+    template <class T> T *dout(size_t off) const { return reinterpret_cast<T *>(g_scratch.dOut + off); }
+    template <class T> T *mapped(size_t off) const { return reinterpret_cast<T *>(g_scratch.hOutDev + off); } // device view of hOut
+    template <class T> const T *hout(size_t off) const { return reinterpret_cast<const T *>(g_scratch.hOut + off); }
+    int upload(size_t bytes) const // bytes: the prefix of the input block in use
+    {
+        ORB_CUDA_OK(cudaMemcpyAsync(g_scratch.dIn, g_scratch.hIn, bytes, cudaMemcpyHostToDevice, g_scratch.stream));
+        return ORBB200_OK;
+    }
+    int download(size_t bytes) const
+    {
+        ORB_CUDA_OK(cudaMemcpyAsync(g_scratch.hOut, g_scratch.dOut, bytes, cudaMemcpyDeviceToHost, g_scratch.stream));
+        return ORBB200_OK;
+    }
+};
 
 // chunking of the database so that the grid is about 4 blocks per SM on 148 SMs
 static void bf_plan(int nq, int ndb, int *groups, int *chunks, int *rowsPerChunk)
@@ -246,20 +315,19 @@ int orbb200_match_candidates(const uint8_t *q, int nq, const uint8_t *t, int nt,
     ORB_ARG_OK(total >= 0 && (total == 0 ? cand_offsets[0] == 0 : csr_valid(cand_offsets, nq, cand_idx, nt)), "candidate lists: offsets not ascending from 0 or index outside [0, nt)");
     int rc = scratch_bind(device);
     if (rc) return rc;
-    void *dq, *dt, *dout, *doffs, *didx;
-    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)std::max(nt, 1) * 32, &dt)) ||
-        (rc = scratch_get(2, (size_t)nq * sizeof(orbb200_top2), &dout)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
-        (rc = scratch_get(4, (size_t)std::max(total, 1) * 4, &didx)))
-        return rc;
+    Pack K;
+    const size_t oq = K.in((size_t)nq * 32), ot = K.in((size_t)std::max(nt, 1) * 32), oo = K.in((size_t)(nq + 1) * 4), oi = K.in((size_t)std::max(total, 1) * 4);
+    const size_t ro = K.out((size_t)nq * sizeof(orbb200_top2));
+    if ((rc = K.reserve())) return rc;
     cudaStream_t st = g_scratch.stream;
-    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
-    if (nt > 0) ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
-    if (total > 0) ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
-    k_match_candidates<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
-                                                            (const int *)didx, (orbb200_top2 *)dout);
-    ORB_CUDA_OK(cudaMemcpyAsync(out, dout, (size_t)nq * sizeof(orbb200_top2), cudaMemcpyDeviceToHost, st));
+    const uint8_t *dq = K.put<uint8_t>(oq, q, (size_t)nq * 32), *dt = K.put<uint8_t>(ot, t, (size_t)std::max(nt, 0) * 32);
+    const int *doffs = K.put<int>(oo, cand_offsets, (size_t)(nq + 1) * 4), *didx = K.put<int>(oi, cand_idx, (size_t)total * 4);
+    if ((rc = K.upload(K.inBytes))) return rc;
+    count_h2d(K.inBytes);
+    k_match_candidates<<<div_up(nq * 32, 256), 256, 0, st>>>(dq, nq, dt, doffs, didx, K.dout<orbb200_top2>(ro));
+    if ((rc = K.download(K.outBytes))) return rc;
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    memcpy(out, K.hout<orbb200_top2>(ro), (size_t)nq * sizeof(orbb200_top2));
     return ORBB200_OK;
 }
 
@@ -274,21 +342,19 @@ int orbb200_candidate_distances(const uint8_t *q, int nq, const uint8_t *t, int 
     ORB_ARG_OK(csr_valid(cand_offsets, nq, cand_idx, nt), "candidate lists: offsets not ascending from 0 or index outside [0, nt)");
     int rc = scratch_bind(device);
     if (rc) return rc;
-    void *dq, *dt, *dout, *doffs, *didx;
-    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)nt * 32, &dt)) ||
-        (rc = scratch_get(2, (size_t)total * 2, &dout)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
-        (rc = scratch_get(4, (size_t)total * 4, &didx)))
-        return rc;
+    Pack K;
+    const size_t oq = K.in((size_t)nq * 32), ot = K.in((size_t)nt * 32), oo = K.in((size_t)(nq + 1) * 4), oi = K.in((size_t)total * 4);
+    const size_t ro = K.out((size_t)total * 2);
+    if ((rc = K.reserve())) return rc;
     cudaStream_t st = g_scratch.stream;
-    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
-    count_h2d((size_t)nq * 36 + (size_t)nt * 32 + (size_t)total * 4);
-    k_candidate_distances<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, nq, (const uint8_t *)dt, (const int *)doffs,
-                                                               (const int *)didx, (unsigned short *)dout);
-    ORB_CUDA_OK(cudaMemcpyAsync(dist, dout, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
+    const uint8_t *dq = K.put<uint8_t>(oq, q, (size_t)nq * 32), *dt = K.put<uint8_t>(ot, t, (size_t)nt * 32);
+    const int *doffs = K.put<int>(oo, cand_offsets, (size_t)(nq + 1) * 4), *didx = K.put<int>(oi, cand_idx, (size_t)total * 4);
+    if ((rc = K.upload(K.inBytes))) return rc;
+    count_h2d(K.inBytes);
+    k_candidate_distances<<<div_up(nq * 32, 256), 256, 0, st>>>(dq, nq, dt, doffs, didx, K.dout<unsigned short>(ro));
+    if ((rc = K.download(K.outBytes))) return rc;
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    memcpy(dist, K.hout<uint16_t>(ro), (size_t)total * 2);
     return ORBB200_OK;
 }
 
@@ -311,33 +377,29 @@ int orbb200_search_triangulation(const uint8_t *q, const float *qxy, const uint8
     for (int i = 0; i < nt; i++) ORB_ARG_OK(tkp[i].octave >= 0 && tkp[i].octave < nlevels, "target keypoint octave outside the level tables");
     int rc = scratch_bind(device);
     if (rc) return rc;
-    void *dq, *dt, *dkp, *dts, *dqxy, *dqs, *doffs, *didx, *dbi, *dbd;
-    if ((rc = scratch_get(0, (size_t)nq * 32, &dq)) || (rc = scratch_get(1, (size_t)nt * 32, &dt)) ||
-        (rc = scratch_get(2, (size_t)nt * sizeof(orbb200_keypoint), &dkp)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &doffs)) ||
-        (rc = scratch_get(4, (size_t)total * 4, &didx)) || (rc = scratch_get(6, (size_t)nt, &dts)) || (rc = scratch_get(7, (size_t)nq * 8, &dqxy)) ||
-        (rc = scratch_get(8, (size_t)nq, &dqs)) || (rc = scratch_get(9, (size_t)nq * 4, &dbi)) || (rc = scratch_get(10, (size_t)nq * 4, &dbd)))
-        return rc;
+    Pack K;
+    const size_t oq = K.in((size_t)nq * 32), ot = K.in((size_t)nt * 32), ok = K.in((size_t)nt * sizeof(orbb200_keypoint)), ots = K.in((size_t)nt),
+                 oxy = K.in((size_t)nq * 8), oqs = K.in((size_t)nq), oo = K.in((size_t)(nq + 1) * 4), oi = K.in((size_t)total * 4);
+    const size_t rbi = K.out((size_t)nq * 4), rbd = K.out((size_t)nq * 4);
+    if ((rc = K.reserve())) return rc;
     cudaStream_t st = g_scratch.stream;
-    ORB_CUDA_OK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dts, tstereo, (size_t)nt, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dqxy, qxy, (size_t)nq * 8, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dqs, qstereo, (size_t)nq, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(doffs, cand_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(didx, cand_idx, (size_t)total * 4, cudaMemcpyHostToDevice, st));
-    count_h2d((size_t)nq * 45 + (size_t)nt * 61 + (size_t)total * 4);
+    const uint8_t *dq = K.put<uint8_t>(oq, q, (size_t)nq * 32), *dt = K.put<uint8_t>(ot, t, (size_t)nt * 32);
+    const orbb200_keypoint *dkp = K.put<orbb200_keypoint>(ok, tkp, (size_t)nt * sizeof(orbb200_keypoint));
+    const uint8_t *dts = K.put<uint8_t>(ots, tstereo, (size_t)nt), *dqs = K.put<uint8_t>(oqs, qstereo, (size_t)nq);
+    const float2 *dqxy = K.put<float2>(oxy, qxy, (size_t)nq * 8);
+    const int *doffs = K.put<int>(oo, cand_offsets, (size_t)(nq + 1) * 4), *didx = K.put<int>(oi, cand_idx, (size_t)total * 4);
+    if ((rc = K.upload(K.inBytes))) return rc;
+    count_h2d(K.inBytes);
     TriangulationParams P;
     memset(&P, 0, sizeof(P));
     for (int i = 0; i < 9; i++) P.F[i] = F12[i];
     P.ex = ex; P.ey = ey; P.thLow = th_low;
     for (int l = 0; l < nlevels; l++) { P.sf[l] = scale_factors[l]; P.sig2[l] = level_sigma2[l]; }
-    k_triangulation_search<<<div_up(nq * 32, 256), 256, 0, st>>>((const uint8_t *)dq, (const float2 *)dqxy, (const uint8_t *)dqs, nq, (const uint8_t *)dt,
-                                                                (const orbb200_keypoint *)dkp, (const uint8_t *)dts, (const int *)doffs,
-                                                                (const int *)didx, P, (int *)dbi, (int *)dbd);
-    ORB_CUDA_OK(cudaMemcpyAsync(best_idx2, dbi, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
-    if (best_dist) ORB_CUDA_OK(cudaMemcpyAsync(best_dist, dbd, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    k_triangulation_search<<<div_up(nq * 32, 256), 256, 0, st>>>(dq, dqxy, dqs, nq, dt, dkp, dts, doffs, didx, P, K.dout<int>(rbi), K.dout<int>(rbd));
+    if ((rc = K.download(K.outBytes))) return rc;
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    memcpy(best_idx2, K.hout<int>(rbi), (size_t)nq * 4);
+    if (best_dist) memcpy(best_dist, K.hout<int>(rbd), (size_t)nq * 4);
     return ORBB200_OK;
 }
 
@@ -354,51 +416,62 @@ static int window_search_impl(const orbb200_keypoint *tkp, const uint8_t *tdesc,
     int rc = scratch_bind(device);
     if (rc) return rc;
     const int nc = cols * rows;
-    void *dkp, *dtd, *dwin, *dqd, *dcs, *dci, *dcnt;
-    if ((rc = scratch_get(0, (size_t)nq * 32, &dqd)) || (rc = scratch_get(1, (size_t)nt * 32, &dtd)) ||
-        (rc = scratch_get(6, (size_t)nt * sizeof(orbb200_keypoint), &dkp)) || (rc = scratch_get(7, (size_t)nq * 20, &dwin)) ||
-        (rc = scratch_get(8, (size_t)(nc + 1) * 4, &dcs)) || (rc = scratch_get(9, (size_t)nt * 4, &dci)) ||
-        (rc = scratch_get(3, (size_t)(nq + 1) * 4, &dcnt)))
+    void *dcs, *dci, *dcnt;
+    if ((rc = scratch_get(8, (size_t)(nc + 1) * 4, &dcs)) || (rc = scratch_get(9, (size_t)nt * 4, &dci)) || (rc = scratch_get(3, (size_t)(nq + 1) * 4, &dcnt)))
         return rc;
+    const int cap = std::max(cand_cap, 0);
+    ORB_ARG_OK(cap == 0 || (cand_idx && dist), "null output");
+    Pack K;
+    const size_t ow = K.in((size_t)nq * 20), oqd = K.in((size_t)nq * 32);
+    const size_t inQueries = K.inBytes;
+    const size_t okp = K.in(resident ? 0 : (size_t)nt * sizeof(orbb200_keypoint)), otd = K.in(resident ? 0 : (size_t)nt * 32);
+    // results are written by the kernels straight into the mapped pinned block: offsets, then candidates and distances up to cap
+    const size_t ro = K.out((size_t)(nq + 1) * 4), rc_ = K.out((size_t)cap * 4), rd = K.out((size_t)cap * 2);
+    if ((rc = K.reserve())) return rc;
     cudaStream_t st = g_scratch.stream;
+    const float *dwin = K.put<float>(ow, windows, (size_t)nq * 20);
+    const uint8_t *dqd = K.put<uint8_t>(oqd, qdesc, (size_t)nq * 32);
+    const orbb200_keypoint *dkp = tkp;
+    const uint8_t *dtd = tdesc;
     if (resident) {
         ORB_ARG_OK(((size_t)tdesc & 15) == 0, "resident descriptors must be 16-byte aligned");
-        dkp = const_cast<orbb200_keypoint *>(tkp);
-        dtd = const_cast<uint8_t *>(tdesc);
+        if ((rc = K.upload(inQueries))) return rc;
+        count_h2d((size_t)nq * 52);
     } else {
-        ORB_CUDA_OK(cudaMemcpyAsync(dkp, tkp, (size_t)nt * sizeof(orbb200_keypoint), cudaMemcpyHostToDevice, st));
-        ORB_CUDA_OK(cudaMemcpyAsync(dtd, tdesc, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+        dkp = K.put<orbb200_keypoint>(okp, tkp, (size_t)nt * sizeof(orbb200_keypoint));
+        dtd = K.put<uint8_t>(otd, tdesc, (size_t)nt * 32);
+        if ((rc = K.upload(K.inBytes))) return rc;
         count_h2d((size_t)nt * (sizeof(orbb200_keypoint) + 32));
+        count_h2d((size_t)nq * 52);
     }
-    ORB_CUDA_OK(cudaMemcpyAsync(dwin, windows, (size_t)nq * 20, cudaMemcpyHostToDevice, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dqd, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
-    count_h2d((size_t)nq * 52);
     WindowParams W;
     memset(&W, 0, sizeof(W));
-    W.G.kp = (const orbb200_keypoint *)dkp; W.G.n = nt;
+    W.G.kp = dkp; W.G.n = nt;
     W.G.minX = minX; W.G.minY = minY; W.G.invW = invW; W.G.invH = invH; W.G.cols = cols; W.G.rows = rows;
     W.G.cellStart = (int *)dcs; W.G.cellItems = (int *)dci;
-    W.win = (const float *)dwin; W.qdesc = (const uint8_t *)dqd; W.tdesc = (const uint8_t *)dtd; W.nq = nq;
+    W.win = dwin; W.qdesc = dqd; W.tdesc = dtd; W.nq = nq;
     W.counts = (int *)dcnt;
-    k_grid_build<<<1, 256, (size_t)(nc + 1) * 4, st>>>(W.G);
+    W.candIdx = K.mapped<int>(rc_); W.dist = K.mapped<unsigned short>(rd); W.cap = cap;
+    {
+        int sortLen;
+        size_t gsmBytes = grid_build_smem(nc, nt, &sortLen);
+        if (gsmBytes > 48 * 1024) { sortLen = 0; gsmBytes = (size_t)(nc + 1) * 4; } // no room for the sort keys: ordered fill by one warp
+        k_grid_build<<<1, GB_THREADS, gsmBytes, st>>>(W.G, sortLen);
+    }
     k_window_count<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
-    k_scan_counts<<<1, 1024, 0, st>>>((int *)dcnt, nq);
-    ORB_CUDA_OK(cudaMemcpyAsync(cand_offsets, dcnt, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, st));
+    k_scan_counts<<<1, 1024, 0, st>>>((int *)dcnt, nq, K.mapped<int>(ro));
+    k_window_fill<<<div_up(nq * 32, 256), 256, 0, st>>>(W); // positions at or beyond cap are dropped
+    ORB_CUDA_OK(cudaGetLastError());
     ORB_CUDA_OK(cudaStreamSynchronize(st));
+    memcpy(cand_offsets, K.hout<int>(ro), (size_t)(nq + 1) * 4);
     const int total = cand_offsets[nq];
     if (total > cand_cap) {
         set_error("orbb200_window_search: %d candidates, capacity is %d", total, cand_cap);
         return ORBB200_ERR_CAPACITY; // cand_offsets is valid: the caller can size the buffers and call again
     }
     if (total == 0) return ORBB200_OK;
-    ORB_ARG_OK(cand_idx && dist, "null output");
-    void *dcand, *ddist;
-    if ((rc = scratch_get(4, (size_t)total * 4, &dcand)) || (rc = scratch_get(2, (size_t)total * 2, &ddist))) return rc;
-    W.candIdx = (int *)dcand; W.dist = (unsigned short *)ddist; W.cap = total;
-    k_window_fill<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
-    ORB_CUDA_OK(cudaMemcpyAsync(cand_idx, dcand, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_OK(cudaMemcpyAsync(dist, ddist, (size_t)total * 2, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_OK(cudaStreamSynchronize(st));
+    memcpy(cand_idx, K.hout<int>(rc_), (size_t)total * 4);
+    memcpy(dist, K.hout<uint16_t>(rd), (size_t)total * 2);
     return ORBB200_OK;
 }
 
@@ -485,9 +558,14 @@ int orbb200_window_search_device(const orbb200_keypoint *tkp_d, const uint8_t *t
     W.G.cellStart = workspace_d; W.G.cellItems = workspace_d + nc + 1;
     W.win = windows_d; W.qdesc = qdesc_d; W.tdesc = tdesc_d; W.nq = nq;
     W.counts = cand_offsets_d; W.candIdx = cand_idx_d; W.dist = dist_d; W.cap = cand_cap;
-    k_grid_build<<<1, 256, (size_t)(nc + 1) * 4, st>>>(W.G);
+    {
+        int sortLen;
+        size_t gsmBytes = grid_build_smem(nc, nt, &sortLen);
+        if (gsmBytes > 48 * 1024) { sortLen = 0; gsmBytes = (size_t)(nc + 1) * 4; } // no room for the sort keys: ordered fill by one warp
+        k_grid_build<<<1, GB_THREADS, gsmBytes, st>>>(W.G, sortLen);
+    }
     k_window_count<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
-    k_scan_counts<<<1, 1024, 0, st>>>(cand_offsets_d, nq);
+    k_scan_counts<<<1, 1024, 0, st>>>(cand_offsets_d, nq, nullptr);
     if (cand_cap > 0) k_window_fill<<<div_up(nq * 32, 256), 256, 0, st>>>(W);
     ORB_CUDA_OK(cudaGetLastError());
     return ORBB200_OK;

@@ -94,6 +94,37 @@ def test_sharded_merge_equals_flat():
     assert np.array_equal(acc, ref_acc) and acc.any() and not acc.all()
 
 
+@pytest.mark.parametrize("nt", [1, 31, 2048, 8192, 8193, 20000])
+def test_window_search_grid_build_paths(nt):
+    """k_grid_build orders a frame's keypoints by sorting (cell, index) keys in shared memory up to 8 192 keypoints and by an
+    ordered one-warp fill beyond: both must reproduce AssignFeaturesToGrid's insertion order (src/Frame.cc:261-279), also for
+    keypoints outside the grid and many keypoints per cell."""
+    rng = np.random.default_rng(nt)
+    w, h = 752.0, 480.0
+    kps = np.zeros(nt, orbb200.KP_DTYPE)
+    kps["x"] = rng.uniform(-20, w + 20, nt).astype(np.float32)
+    kps["y"] = rng.uniform(-20, h + 20, nt).astype(np.float32)
+    kps["x"][: nt // 3] = np.float32(100.0) + rng.uniform(0, 5, nt // 3).astype(np.float32)  # a crowded cell
+    kps["y"][: nt // 3] = np.float32(100.0)
+    kps["octave"] = rng.integers(0, 8, nt)
+    desc = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    invW, invH = np.float32(64) / np.float32(w), np.float32(48) / np.float32(h)
+    nq = 300
+    win = np.zeros((nq, 5), np.float32)
+    win[:, 0], win[:, 1] = rng.uniform(0, w, nq), rng.uniform(0, h, nq)
+    win[:40, 0], win[:40, 1] = 102.0, 100.0
+    win[:, 2] = rng.choice([5.0, 20.0, 60.0], nq)
+    win[:, 3], win[:, 4] = -1, -1
+    qdesc = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    offs, idx, dist = orbb200.ORBmatcher().window_search(kps, desc, (0.0, 0.0, float(invW), float(invH), 64, 48), win, qdesc)
+    start, items = ref_cpu.assign_grid(kps, 0.0, 0.0, invW, invH, 64, 48)
+    for q in range(nq):
+        ref = ref_cpu.features_in_area(kps, start, items, 0.0, 0.0, invW, invH, win[q, 0], win[q, 1], win[q, 2], -1, -1, 64, 48)
+        assert np.array_equal(idx[offs[q]:offs[q + 1]], ref), (q, idx[offs[q]:offs[q + 1]][:8], ref[:8])
+        if len(ref):
+            assert np.array_equal(dist[offs[q]:offs[q + 1]], np.unpackbits(desc[ref] ^ qdesc[q], axis=1).sum(axis=1))
+
+
 def test_candidate_distances_equal_oracle_and_reference():
     """orbb200_candidate_distances (k_candidate_distances): the distance step of both SearchByBoW overloads and of
     SearchForTriangulation (src/ORBmatcher.cc:214-244, 626-650, 780-815) on random CSR candidate lists -- empty lists, lists

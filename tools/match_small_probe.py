@@ -30,8 +30,8 @@ win[:, 2] = 15.0 * np.float32(1.2) ** kps["octave"][src]
 win[:, 3] = kps["octave"][src] - 1; win[:, 4] = kps["octave"][src] + 1
 grid = (0.0, 0.0, 64.0 / w, 48.0 / h, 64, 48)
 qd = desc[src].copy()
-offs, idx, dist = m.window_search(kps, desc, grid, win, qd, cap=200)
-t = timed(lambda: m.window_search(kps, desc, grid, win, qd, cap=200))
+offs, idx, dist = m.window_search(kps, desc, grid, win, qd, cap=64 * nq)
+t = timed(lambda: m.window_search(kps, desc, grid, win, qd, cap=64 * nq))
 res["window_search"] = {"queries": nq, "targets": int(len(kps)), "pairs": int(offs[-1]), "us_per_call": t * 1e6, "pairs_per_s": offs[-1] / t,
                         "calls_per_s": 1 / t}
 # --- candidate lists (SearchByBoW shape: 2000 queries x ~12 candidates) -----------------------------------------------------------------
