@@ -366,13 +366,18 @@ def run_b200(args, rank, world, local_rank):
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from this round's committed `ncu --set full`
     # capture of the same command (profiles/r2_traffic.json, written by tools/ncu_traffic.py); null when there is no capture
     # for this kernel and batch -- nothing is hard-coded here
-    traffic = None
+    traffic, issue = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         ent = tj.get({"pyramid": "k_pyramid_resize", "fast_cells": "k_fast_strips", "octree_select": "k_octree_select", "blur7": "k_blur7",
                       "orient_describe": "k_orient_describe"}[dom])
         if ent and int(ent.get("images_per_launch", -1)) == B:
             traffic = int(ent["dram_bytes_per_launch"])
+            # what really bounds the kernel, from the same capture: issue slots and the busiest pipes
+            issue = {k: ent[k] for k in ("issue_slots_busy_pct", "sm_throughput_pct", "alu_pipe_pct", "l1tex_throughput_pct",
+                                         "lsu_shared_wavefronts_pct", "dram_throughput_pct", "warp_instructions", "ipc_active",
+                                         "registers_per_thread", "achieved_occupancy_pct") if k in ent}
+            issue["source"] = "profiles/" + str(ent.get("report", "r2_traffic.json")) + " via profiles/r2_traffic.json (ncu --set full, one launch)"
     except Exception:
         pass
     kernel_names = {"pyramid": "k_pyramid_resize", "fast_cells": "k_fast_strips", "octree_select": "k_octree_select",
@@ -380,8 +385,9 @@ def run_b200(args, rank, world, local_rank):
     roofline = {
         "kernel": kernel_names.get(dom, "k_" + dom), "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
         "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-        "bound_note": "reported against HBM as the contract asks; ncu (profiles/r2_fast_strips_full_details.txt) shows the kernel bound by "
-                      "the shared-memory pipe (80 % L1/TEX wavefronts) with issue slots 66 % and the integer ALU pipe 62 % busy, DRAM < 4 %",
+        "issue": issue,
+        "bound_note": "reported against HBM as the contract asks; the ncu capture (profiles/r2_extract_kernels_full_details.txt, figures in "
+                      "`issue`) shows the kernel bound by the shared-memory pipe / issue slots, DRAM at a few percent",
         "launches_per_step": dom_launches, "ms_per_step": stage_ms[dom], "algorithmic_bytes_per_step": dom_bytes,
         "stage_ms_per_step": stage_ms,
         "path": {"algorithmic_bytes_per_image": abytes_img, "achieved": value / world * abytes_img / 1e9,

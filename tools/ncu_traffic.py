@@ -23,9 +23,33 @@ for rep in sys.argv[2:]:
     def to_bytes(v, u):
         v = float(v.replace(",", ""))
         return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
+    # utilisation figures bench.py quotes as roofline.issue (first header that matches each substring)
+    want = {"issue_slots_busy_pct": ["sm__inst_issued.avg.pct_of_peak_sustained_active", "sm__issue_active.avg.pct"],
+            "sm_throughput_pct": ["sm__throughput.avg.pct_of_peak_sustained_elapsed"],
+            "alu_pipe_pct": ["sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__pipe_alu_cycles_active.avg.pct"],
+            "l1tex_throughput_pct": ["l1tex__throughput.avg.pct_of_peak_sustained_active", "l1tex__throughput.avg.pct"],
+            "lsu_shared_wavefronts_pct": ["l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed"],
+            "dram_throughput_pct": ["gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct"],
+            "warp_instructions": ["smsp__inst_executed.sum", "sm__inst_executed.sum"],
+            "ipc_active": ["sm__inst_executed.avg.per_cycle_active"],
+            "registers_per_thread": ["launch__registers_per_thread"],
+            "achieved_occupancy_pct": ["sm__warps_active.avg.pct_of_peak_sustained_active"]}
+    cols = {}
+    for key, subs in want.items():
+        for sub in subs:
+            hit = [i for i, h in enumerate(hdr) if h.startswith(sub)]
+            if hit:
+                cols[key] = hit[0]
+                break
     for r in rows[2:]:
         name = r[ik].split("(")[0].split("::")[-1]
-        res[name] = {"dram_bytes_per_launch": int(to_bytes(r[ir], units[ir]) + to_bytes(r[iw], units[iw])), "images_per_launch": imgs,
-                     "duration": r[it] + " " + units[it], "report": os.path.basename(rep)}
+        ent = {"dram_bytes_per_launch": int(to_bytes(r[ir], units[ir]) + to_bytes(r[iw], units[iw])), "images_per_launch": imgs,
+               "duration": r[it] + " " + units[it], "report": os.path.basename(rep)}
+        for key, i in cols.items():
+            try:
+                ent[key] = float(r[i].replace(",", ""))
+            except ValueError:
+                pass
+        res[name] = ent
 json.dump(res, open(out_path, "w"), indent=1)
 print(json.dumps(res, indent=1))
