@@ -1,5 +1,5 @@
 // describe_kernel.cuh -- E6 + E8 + E9: IC_Angle orientation (src/ORBextractor.cc:83-111), 256-bit rBRIEF
-// (:116-157) and output assembly (:1288-1338) in one kernel; a warp walks DS_KPW selected keypoints.
+// (:116-157) and output assembly (:1288-1338) in one kernel; a warp walks kpw selected keypoints.
 //
 // Round-1 ncu of the first version: 1430 warp instructions per keypoint, long-scoreboard bound (16 scattered byte
 // gathers per lane = 512 L1 sectors per keypoint), XU pipe busy with I2F/F2I; second version (smem-staged blurred
@@ -21,7 +21,9 @@
 
 namespace orbb200 {
 
-constexpr int DS_WARPS = 8, DS_KPW = 4;      // warps per block, keypoint slots per warp
+constexpr int DS_WARPS = 8;                   // warps per block
+constexpr int DS_KPW_MAX = 16, DS_KPW_MIN = 2; // keypoint slots per warp: 16 for batches (block prologue amortised, the next keypoint's patches always in
+                                              // flight: 0.70 ms at 4 -> 0.58 ms at 16 per 320 KITTI images), fewer when that would leave SMs without a block
 constexpr int DS_PROWS = 37, DS_PPITCH = 64; // staged blurred patch: rows y-18..y+18, 64 bytes from (x-18) & ~15
 constexpr int DS_RROWS = 32, DS_RPITCH = 48; // staged un-blurred patch: rows y-15..y+15 (+1 pad), 48 bytes from (x-15) & ~15
 
@@ -84,6 +86,18 @@ __device__ __forceinline__ int cv_round_magic(float v)
     return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
 }
 
+// 16-byte asynchronous copy global -> shared, bypassing L1 (each patch is read once); !in: 16 zero bytes, nothing is read
+__device__ __forceinline__ void cp_async16_zfill(void *smem, const void *gmem, bool in)
+{
+    const unsigned int sa = (unsigned int)__cvta_generic_to_shared(smem);
+    const int n = in ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gmem), "r"(n));
+}
+
+__device__ __forceinline__ void ds_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void ds_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+constexpr size_t DS_SMEM = 8 * 32 * 16 + (size_t)DS_WARPS * 2 * (DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
+
 __device__ __forceinline__ int dp4a_us(unsigned int a, unsigned int b, int c)
 {
     int d;
@@ -110,11 +124,13 @@ template <int KW> __device__ __forceinline__ void disc_row_sums(const uint4 &q0,
     }
 }
 
-__global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __grid_constant__ ExtractParams P)
+__global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __grid_constant__ ExtractParams P, int kpw)
 {
-    __shared__ __align__(16) float4 sPat[8 * 32];                               // [bit k of the byte][lane]
-    __shared__ __align__(16) uint8_t sPatch[DS_WARPS][DS_PROWS * DS_PPITCH];
-    __shared__ __align__(16) uint8_t sRaw[DS_WARPS][DS_RROWS * DS_RPITCH];
+    extern __shared__ __align__(16) unsigned char ds_smem[];
+    float4 *sPat = reinterpret_cast<float4 *>(ds_smem);                                // [bit k of the byte][lane]
+    // per warp, double buffered (this keypoint / the next one in flight): blurred patch, un-blurred patch
+    uint8_t *sPatchW = ds_smem + 8 * 32 * sizeof(float4) + (size_t)(threadIdx.x >> 5) * 2 * (DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
+    uint8_t *sRawW = sPatchW + 2 * DS_PROWS * DS_PPITCH;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         // pattern pair i belongs to descriptor byte i / 8 (= lane), bit i % 8
         sPat[(i & 7) * 32 + (i >> 3)] = make_float4((float)c_pattern[i][0], (float)c_pattern[i][1], (float)c_pattern[i][2], (float)c_pattern[i][3]);
@@ -151,59 +167,66 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __gr
     }
     __syncthreads();
 
-    uint8_t *patch = sPatch[wid], *raw = sRaw[wid];
-    const int slot0 = (blockIdx.x * DS_WARPS + wid) * DS_KPW;
-    for (int kpi = 0; kpi < DS_KPW; kpi++) {
-        const int slot = slot0 + kpi;
-        if (slot >= P.nodeTotal) break;
+    // ---- a warp walks its DS_KPW keypoint slots with the patches of the NEXT keypoint in flight (cp.async, 16 bytes per lane and
+    //      request, straight into the other half of the warp's double-buffered shared-memory patches) while it works on this one:
+    //      the kernel used to spend a third of its issue slots waiting for the eight staging loads of each keypoint
+    struct Kp { int valid, l, outIdx, x, y, resp; };
+    auto decode = [&](int slot) {
+        Kp k;
+        k.valid = 0; k.l = 0; k.outIdx = 0; k.x = 0; k.y = 0; k.resp = 0;
+        if (slot >= P.nodeTotal) return k;
         const int l = __popc(__ballot_sync(0xffffffffu, slot >= tNodeOff)) - 1; // nodeOff ascends with the level
         const int pos = slot - __shfl_sync(0xffffffffu, tNodeOff, l);
-        if (pos >= __shfl_sync(0xffffffffu, tCnt, l)) continue;
-        const int outIdx = __shfl_sync(0xffffffffu, tOutOff, l) + pos;
-        if (outIdx >= P.cap) continue;
-        const int gpitch = __shfl_sync(0xffffffffu, tPitch, l);
-        const unsigned int imgOff = __shfl_sync(0xffffffffu, tImgOff, l);
+        const int cnt = __shfl_sync(0xffffffffu, tCnt, l), oo = __shfl_sync(0xffffffffu, tOutOff, l);
+        if (pos >= cnt || oo + pos >= P.cap) return k;
         const uint32_t packed = P.lvlKp[(size_t)b * P.nodeTotal + slot];
-        const int x = (int)(packed & 0xFFF) + 16, y = (int)((packed >> 12) & 0xFFF) + 16;
-        const int resp = (int)(packed >> 24);
-
-        // ---- stage the blurred 37 x 37 patch (rows y-18..y+18, 16-byte chunks from (x-18) & ~15) and the un-blurred
-        //      31 x 31 one (rows y-15..y+15 from (x-15) & ~15): all 8 loads of a lane in flight together
+        k.valid = 1; k.l = l; k.outIdx = oo + pos;
+        k.x = (int)(packed & 0xFFF) + 16; k.y = (int)((packed >> 12) & 0xFFF) + 16; k.resp = (int)(packed >> 24);
+        return k;
+    };
+    // blurred 37 x 37 patch (rows y-18..y+18, 16-byte chunks from (x-18) & ~15) and un-blurred 31 x 31 one (rows y-15..y+15 from
+    // (x-15) & ~15, row 31 = zeros); chunks beyond the row pitch are zero-filled (src-size 0)
+    auto prefetch = [&](const Kp &k, uint8_t *patch, uint8_t *raw) {
+        const int gpitch = __shfl_sync(0xffffffffu, tPitch, k.l);
+        const unsigned int imgOff = __shfl_sync(0xffffffffu, tImgOff, k.l);
         const uint8_t *bl = P.blur + (size_t)b * P.pyrStride + imgOff;
-        const uint8_t *img = l ? P.pyr + (size_t)b * P.pyrStride + imgOff : P.l0 + (size_t)b * P.l0ImgStride;
-        const int ipitch = l ? gpitch : P.l0Pitch;
-        const int px0 = (x - 18) & ~15, px1 = (x - 15) & ~15;
-        __syncwarp(); // every lane is done with the previous keypoint's patches
-        {
-            uint4 v[5], u[3];
+        const uint8_t *img = k.l ? P.pyr + (size_t)b * P.pyrStride + imgOff : P.l0 + (size_t)b * P.l0ImgStride;
+        const int ipitch = k.l ? gpitch : P.l0Pitch;
+        const int px0 = (k.x - 18) & ~15, px1 = (k.x - 15) & ~15;
 #pragma unroll
-            for (int i = 0; i < 5; i++) {
-                const int idx = lane + 32 * i; // chunk index: row = idx / 4, chunk = idx % 4
-                const int r = idx >> 2, ch = idx & 3;
-                const int gx = px0 + (ch << 4);
-                v[i] = make_uint4(0, 0, 0, 0);
-                if (idx < DS_PROWS * 4 && gx < gpitch) v[i] = ldg_nc_v4(bl + (size_t)(y - 18 + r) * gpitch + gx);
-            }
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-                const int idx = lane + 32 * i; // row = idx / 3, chunk = idx % 3
-                const int r = (idx * 171) >> 9, ch = idx - 3 * r;
-                const int gx = px1 + (ch << 4);
-                u[i] = make_uint4(0, 0, 0, 0);
-                if (idx < 31 * 3 && gx < ipitch) u[i] = ldg_nc_v4(img + (size_t)(y - 15 + r) * ipitch + gx);
-            }
-#pragma unroll
-            for (int i = 0; i < 5; i++) {
-                const int idx = lane + 32 * i;
-                if (idx < DS_PROWS * 4) *reinterpret_cast<uint4 *>(patch + (idx >> 2) * DS_PPITCH + ((idx & 3) << 4)) = v[i];
-            }
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-                const int idx = lane + 32 * i;
-                if (idx < 32 * 3) *reinterpret_cast<uint4 *>(raw + idx * 16) = u[i]; // row-major 48-byte rows; row 31 = zeros
+        for (int i = 0; i < 5; i++) {
+            const int idx = lane + 32 * i; // chunk index: row = idx / 4, chunk = idx % 4
+            const int r = idx >> 2, gx = px0 + ((idx & 3) << 4);
+            if (idx < DS_PROWS * 4) {
+                const bool in = gx < gpitch;
+                cp_async16_zfill(patch + r * DS_PPITCH + ((idx & 3) << 4), bl + (size_t)(k.y - 18 + r) * gpitch + (in ? gx : 0), in);
             }
         }
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const int idx = lane + 32 * i; // row = idx / 3, chunk = idx % 3
+            const int r = (idx * 171) >> 9, gx = px1 + ((idx - 3 * r) << 4);
+            const bool in = idx < 31 * 3 && gx < ipitch;
+            cp_async16_zfill(raw + idx * 16, img + (size_t)(k.y - 15 + (in ? r : 0)) * ipitch + (in ? gx : 0), in);
+        }
+        ds_cp_commit();
+    };
+    const int slot0 = (blockIdx.x * DS_WARPS + wid) * kpw;
+    Kp cur = decode(slot0);
+    if (cur.valid) prefetch(cur, sPatchW, sRawW);
+    for (int kpi = 0; kpi < kpw; kpi++) {
+        Kp nxt;
+        nxt.valid = 0;
+        if (kpi + 1 < kpw) nxt = decode(slot0 + kpi + 1);
+        // every lane is done with the buffer the next keypoint goes to (it held keypoint kpi - 1)
         __syncwarp();
+        if (nxt.valid) prefetch(nxt, sPatchW + ((kpi + 1) & 1) * DS_PROWS * DS_PPITCH, sRawW + ((kpi + 1) & 1) * DS_RROWS * DS_RPITCH);
+        if (!cur.valid) { cur = nxt; continue; }
+        if (nxt.valid) ds_cp_wait<1>(); else ds_cp_wait<0>();
+        __syncwarp();
+        const uint8_t *patch = sPatchW + (kpi & 1) * DS_PROWS * DS_PPITCH, *raw = sRawW + (kpi & 1) * DS_RROWS * DS_RPITCH;
+        const int l = cur.l, outIdx = cur.outIdx, x = cur.x, y = cur.y, resp = cur.resp;
+        const int px0 = (x - 18) & ~15, px1 = (x - 15) & ~15;
 
         // ---- E6: intensity-centroid moments over the radius-15 disc of the UN-blurred level; lane <-> row v
         int m10, m01;
@@ -262,6 +285,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __gr
             }
             reinterpret_cast<float *>(P.kps + (size_t)b * P.cap + outIdx)[lane] = f;
         }
+        cur = nxt;
     }
 }
 

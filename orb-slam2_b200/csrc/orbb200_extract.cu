@@ -54,6 +54,7 @@ static int opt_in_shared_memory(int device)
     const int kMax = 200 * 1024;
     ORB_CUDA_OK(cudaFuncSetAttribute(k_pyramid_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS_BIG, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     done[device] = true;
