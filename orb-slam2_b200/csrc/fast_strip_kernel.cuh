@@ -51,7 +51,7 @@ constexpr int FS_LISTCAP = 512;   // corner list entries per warp; a warp that f
 
 __host__ __device__ inline size_t fast_strip_smem(int rows)
 {
-    return (size_t)rows * FS_SPW * 4 * 2 + (size_t)(rows - 4) * FS_MAPPITCH;
+    return (size_t)rows * FS_SPW * 4 + (size_t)(rows - 4) * FS_MAPPITCH;
 }
 
 __device__ __forceinline__ unsigned int widen_lo(unsigned int w) { return __byte_perm(w, 0u, 0x4140); }
@@ -70,12 +70,12 @@ __device__ __forceinline__ unsigned int neg_mask2(unsigned int w)
 }
 
 struct FsCtx {
-    const unsigned int *evenCopy, *oddCopy; // widened copies serving the even / odd ring offsets
-    const unsigned short *hU;               // copy U as 16-bit pixels, pitch 2 * FS_SPW
+    const unsigned int *pairs;              // the widened copy: word k of a row = tile pixels (e0 + 2k, e0 + 2k + 1), e0 = parity of interior x = 0
+    const unsigned short *hU;               // the same copy as 16-bit pixels, pitch 2 * FS_SPW
     unsigned char *sM;                      // score map
     unsigned short *queue;                  // this warp's ring queue
     unsigned short *corners;                // this warp's list of the pixels it scored >= th (input of the NMS)
-    int cofs, oofs, a;
+    int cofs, a;                            // word of interior pair 0; 16-bit index of interior x = 0
 };
 
 // Phase B on up to 64 queue entries starting at the ring head: exact score, stored where it reaches th
@@ -157,18 +157,17 @@ __device__ __forceinline__ void fs_scan(const FsCtx &c, int x0, int x1, int ih, 
         const int x = 2 * xl;
         unsigned int vmask = 0u;
         if (inr) vmask = ((x >= x0) ? 0x0000FFFFu : 0u) | ((x + 1 < x1) ? 0xFFFF0000u : 0u);
-        const unsigned int *pa = c.evenCopy + (row0 + 3) * FS_SPW + xl + c.cofs;
-        const unsigned int *pb = c.oddCopy + (row0 + 3) * FS_SPW + xl + c.oofs;
+        const unsigned int *pa = c.pairs + (row0 + 3) * FS_SPW + xl + c.cofs;
         unsigned int e = (unsigned int)x | ((unsigned int)row0 << 8);
-        for (int y = row0; y < ih; y += rowStep, pa += rowStep * FS_SPW, pb += rowStep * FS_SPW, e += (unsigned int)rowStep << 8) {
+        for (int y = row0; y < ih; y += rowStep, pa += rowStep * FS_SPW, e += (unsigned int)rowStep << 8) {
             const unsigned int v = pa[0];
             // every 9-arc holds ring pixel k or k + 8 for EVERY k; the four even pairs (compass + diagonals: 8 loads instead of 16)
             // already reject ~76 % of the pixels at th = 20 (all eight: 81 %), and the exact network of Phase B costs less than
             // the eight loads and sixteen min/max saved on every pixel (measured: 1.78 -> 1.71 ms; the two compass pairs alone: 1.79 ms)
             const unsigned int r0 = pa[3 * FS_SPW];        // ( 0, 3)
             const unsigned int r8 = pa[-3 * FS_SPW];       // ( 0,-3)
-            const unsigned int r4 = pb[2];                 // ( 3, 0)
-            const unsigned int r12 = pb[-1];               // (-3, 0)
+            const unsigned int r4 = __byte_perm(pa[1], pa[2], 0x5432);    // ( 3, 0): odd offset = second pixel of word + 1, first of word + 2
+            const unsigned int r12 = __byte_perm(pa[-2], pa[-1], 0x5432); // (-3, 0)
             const unsigned int r2 = pa[2 * FS_SPW + 1];    // ( 2, 2)
             const unsigned int r6 = pa[-2 * FS_SPW + 1];   // ( 2,-2)
             const unsigned int r10 = pa[-2 * FS_SPW - 1];  // (-2,-2)
@@ -254,12 +253,11 @@ __device__ __forceinline__ unsigned int fs_row_bits(const unsigned int *bitmap, 
     return w;
 }
 
-__global__ void __launch_bounds__(FS_THREADS, 768 / FS_THREADS) k_fast_strips(const __grid_constant__ ExtractParams P, int rowsCap)
+__global__ void __launch_bounds__(FS_THREADS, 896 / FS_THREADS) k_fast_strips(const __grid_constant__ ExtractParams P, int rowsCap)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
-    unsigned int *sU = reinterpret_cast<unsigned int *>(fsm);
-    unsigned int *sS = sU + rowsCap * FS_SPW;
-    unsigned char *sM = reinterpret_cast<unsigned char *>(sS + rowsCap * FS_SPW); // [(rowsCap - 4)][FS_MAPPITCH]
+    unsigned int *sU = reinterpret_cast<unsigned int *>(fsm);                     // [rowsCap][FS_SPW] the widened ROI
+    unsigned char *sM = reinterpret_cast<unsigned char *>(sU + rowsCap * FS_SPW); // [(rowsCap - 4)][FS_MAPPITCH]
     __shared__ unsigned short sQ[FS_WARPS][FS_QCAP];
     __shared__ unsigned int sBits[(FS_MAXROWS - 4) * FS_BMW];
     __shared__ unsigned char sSeam[FS_MAXIW + 16];
@@ -283,14 +281,20 @@ __global__ void __launch_bounds__(FS_THREADS, 768 / FS_THREADS) k_fast_strips(co
     const uint8_t *img;
     if ((r1.z & 15u) == 0u) { pitch = P.l0Pitch; valid = P.l0Valid; img = P.l0 + (size_t)b * P.l0ImgStride; }
     else { pitch = (int)(r0.w & 0xFFFFu); valid = pitch; img = P.pyr + (size_t)b * P.pyrStride + r0.z; }
-    const int xb = iniX & ~15;
-    const int chunks = (((maxX - xb) + 15) & ~15) >> 4; // <= 12
+    // tile origin: 16-byte aligned, and such that the ring of interior x = 0 (tile column a - 3) stays inside the widened copy,
+    // whose first pixel is tile column e0 = a & 1
+    int xb = iniX & ~15;
+    if (iniX - xb == 0) xb -= 16;                       // a would be 3 (odd): column 0 would be missing; iniX >= 16, so xb stays >= 0
+    const int chunks = (((maxX - xb) + 15) & ~15) >> 4; // <= FS_SPW / 8
     const int a = iniX + 3 - xb;                        // tile column of interior x = 0
+    const int e0 = a & 1;
     const int iw = rw - 6, ih = rh - 6;
-    // ---- stage the ROI, widened to 16 bit: U[k] = pixels (2k, 2k+1), S[k] = pixels (2k+1, 2k+2) of the tile row
+    // ---- stage the ROI widened to 16 bit, ONE copy: word k of a row = tile pixels (e0 + 2k, e0 + 2k + 1), so that the interior
+    //      pixel pairs (2j, 2j + 1) are whole words.  (A second copy of the other parity served the odd ring offsets with plain
+    //      loads; it cost a third of the block's shared memory -- 5 blocks per SM instead of 7 -- and half of the staging work.)
     {
         const bool vec = ((((size_t)img) | (size_t)pitch) & 15) == 0;
-        const unsigned int magic = r2.z; // ceil(65536 / chunks): i / chunks for i < 66 * 12
+        const unsigned int magic = r2.z; // ceil(65536 / chunks), chunks as computed above (orbb200_extract.cu): i / chunks for i < 66 * 12
         for (int i = tid; i < rh * chunks; i += FS_THREADS) {
             const int r = (int)(((unsigned int)i * magic) >> 16), ch = i - r * chunks, x = xb + (ch << 4);
             const uint8_t *src = img + (size_t)(iniY + r) * pitch + x;
@@ -304,21 +308,25 @@ __global__ void __launch_bounds__(FS_THREADS, 768 / FS_THREADS) k_fast_strips(co
                 for (int k = 0; k < 16; k++)
                     if (x + k < gw) wd[k >> 2] |= (unsigned int)__ldg(src + k) << ((k & 3) * 8);
             }
-            wd[4] = (x + 16 < gw) ? (unsigned int)__ldg(src + 16) : 0u;
-            unsigned int U[8], S[8];
+            unsigned int E[8];
+            if (e0) {
+                wd[4] = (x + 16 < gw) ? (unsigned int)__ldg(src + 16) : 0u;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                U[2 * j] = widen_lo(wd[j]);
-                U[2 * j + 1] = widen_hi(wd[j]);
-                const unsigned int sh = __funnelshift_r(wd[j], wd[j + 1], 8);
-                S[2 * j] = widen_lo(sh);
-                S[2 * j + 1] = widen_hi(sh);
+                for (int j = 0; j < 4; j++) {
+                    const unsigned int sh = __funnelshift_r(wd[j], wd[j + 1], 8);
+                    E[2 * j] = widen_lo(sh);
+                    E[2 * j + 1] = widen_hi(sh);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    E[2 * j] = widen_lo(wd[j]);
+                    E[2 * j + 1] = widen_hi(wd[j]);
+                }
             }
-            uint4 *rowU = reinterpret_cast<uint4 *>(sU + r * FS_SPW + 8 * ch), *rowS = reinterpret_cast<uint4 *>(sS + r * FS_SPW + 8 * ch);
-            rowU[0] = make_uint4(U[0], U[1], U[2], U[3]);
-            rowU[1] = make_uint4(U[4], U[5], U[6], U[7]);
-            rowS[0] = make_uint4(S[0], S[1], S[2], S[3]);
-            rowS[1] = make_uint4(S[4], S[5], S[6], S[7]);
+            uint4 *rowE = reinterpret_cast<uint4 *>(sU + r * FS_SPW + 8 * ch);
+            rowE[0] = make_uint4(E[0], E[1], E[2], E[3]);
+            rowE[1] = make_uint4(E[4], E[5], E[6], E[7]);
         }
     }
     // zero the score map (rows 0 .. ih + 1: the border rows included), the survivor bits; seam flags of every interior column
@@ -329,11 +337,9 @@ __global__ void __launch_bounds__(FS_THREADS, 768 / FS_THREADS) k_fast_strips(co
         sSeam[x] = (unsigned char)((xc == 0 ? 1 : 0) | ((xc == wCell - 1 || x == iw - 1) ? 2 : 0)); // bit 0 / 1: left / right neighbour is another cell
     }
     FsCtx c;
-    c.evenCopy = (a & 1) ? sS : sU;
-    c.oddCopy = (a & 1) ? sU : sS;
-    c.cofs = (a & 1) ? ((a - 1) >> 1) : (a >> 1);
-    c.oofs = (a & 1) ? c.cofs : c.cofs - 1;
-    c.a = a;
+    c.pairs = sU;
+    c.cofs = (a - e0) >> 1;
+    c.a = a - e0;
     c.hU = reinterpret_cast<const unsigned short *>(sU);
     c.sM = sM;
     c.queue = sQ[wid];

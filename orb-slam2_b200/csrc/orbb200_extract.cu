@@ -225,7 +225,8 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
                         const int iniX = 16 + j0 * g.wCell;
                         const int maxX = nAct ? std::min(iniX + nAct * g.wCell + 6, maxBX) : iniX;
                         const int rw = nAct ? maxX - iniX : 0, rh = nAct ? maxY - iniY : 0;
-                        const int chunks = rw ? ((((maxX - (iniX & ~15)) + 15) & ~15) >> 4) : 1;
+                        const int xbTile = (iniX & 15) ? (iniX & ~15) : iniX - 16; // tile origin of k_fast_strips
+                        const int chunks = rw ? ((((maxX - xbTile) + 15) & ~15) >> 4) : 1;
                         if (rw - 6 > FS_MAXIW || chunks > FS_SPW / 8) { set_error("internal: FAST strip too wide (%d px)", rw); return ORBB200_ERR_ARG; }
                         strips.push_back(make_uint4((unsigned)iniX | ((unsigned)iniY << 16), (unsigned)rw | ((unsigned)rh << 16), g.imgOff,
                                                     (unsigned)g.pitch | ((unsigned)g.w << 16)));
