@@ -37,6 +37,10 @@ namespace orbb200 {
 #define ORBB200_FS_THREADS 128
 #endif
 constexpr int FS_THREADS = ORBB200_FS_THREADS, FS_WARPS = FS_THREADS / 32;
+#ifndef ORBB200_FS_MINBLOCKS
+#define ORBB200_FS_MINBLOCKS 8
+#endif
+constexpr int FS_MINBLOCKS = ORBB200_FS_MINBLOCKS; // blocks per SM the register allocation aims at
 #ifndef ORBB200_FS_MAXIW
 #define ORBB200_FS_MAXIW 128
 #endif
@@ -253,7 +257,7 @@ __device__ __forceinline__ unsigned int fs_row_bits(const unsigned int *bitmap, 
     return w;
 }
 
-__global__ void __launch_bounds__(FS_THREADS, 896 / FS_THREADS) k_fast_strips(const __grid_constant__ ExtractParams P, int rowsCap)
+__global__ void __launch_bounds__(FS_THREADS, FS_MINBLOCKS) k_fast_strips(const __grid_constant__ ExtractParams P, int rowsCap)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
     unsigned int *sU = reinterpret_cast<unsigned int *>(fsm);                     // [rowsCap][FS_SPW] the widened ROI
