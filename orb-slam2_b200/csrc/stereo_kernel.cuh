@@ -42,7 +42,8 @@ struct StereoParams {
     float *uRight, *depth;
     int *sad; // SAD distance per left keypoint, -1 when no depth
     // row buckets of the right keypoints (:594-604): rowStart[pair][nRows+1], rowList[pair][rowListStride]
-    int *rowStart, *rowList;
+    int *rowStart;
+    int2 *rowList; // entry = (iR | octave << 24, float bits of the keypoint's x): the matcher's gates need no second gather
     size_t rowListStride;
     size_t outStride; // per-pair stride of uRight / depth / sad
     int cap;          // keypoint capacity per image (counts are clamped to it)
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(512) k_stereo_rows(const __grid_constant__ Ste
     const StereoSide SR = stereo_side(P.R, pair);
     const int nR = min(*SR.n, P.cap), nRows = P.nRows;
     int *rowStart = P.rowStart + (size_t)pair * (nRows + 1);
-    int *rowList = P.rowList + (size_t)pair * P.rowListStride;
+    int2 *rowList = P.rowList + (size_t)pair * P.rowListStride;
     for (int r = tid; r < nRows; r += NT) srow[r] = 0;
     __syncthreads();
     for (int iR = tid; iR < nR; iR += NT) {
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(512) k_stereo_rows(const __grid_constant__ Ste
         const int maxr = min((int)ceilf(__fadd_rn(kR.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kR.y, r)), 0);
         for (int yi = minr; yi <= maxr; yi++) {
             const int pos = atomicAdd(&srow[yi], 1);
-            if ((size_t)pos < P.rowListStride) rowList[pos] = iR;
+            if ((size_t)pos < P.rowListStride) rowList[pos] = make_int2(iR | (kR.octave << 24), __float_as_int(kR.x));
         }
     }
 }
@@ -119,30 +120,32 @@ __global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ St
     Top2 t;
     top2_init(t);
     t.d1 = 100; // bestDist starts at TH_HIGH (:633)
+    float bestX = 0.f;
     if (row >= 0 && row < P.nRows && !(maxU < 0)) {
         const Desc dL = load_desc(SL.desc + (size_t)iL * 32);
         const int *rowStart = P.rowStart + (size_t)pair * (P.nRows + 1);
-        const int *rowList = P.rowList + (size_t)pair * P.rowListStride;
+        const int2 *rowList = P.rowList + (size_t)pair * P.rowListStride;
         const int c0 = rowStart[row], c1 = min(rowStart[row + 1], (int)P.rowListStride);
         for (int c = c0 + lane; c < c1; c += 32) {
-            const int iR = rowList[c];
-            const int octR = SR.kps[iR].octave;
+            const int2 ent = rowList[c];
+            const int iR = ent.x & 0xFFFFFF, octR = ent.x >> 24;
             if (octR < levelL - 1 || octR > levelL + 1) continue;
-            const float uR = SR.kps[iR].x;
+            const float uR = __int_as_float(ent.y);
             if (uR >= minU && uR <= maxU) {
                 const int d = hamming(dL, load_desc(SR.desc + (size_t)iR * 32));
-                if (d < t.d1 || (d == t.d1 && t.i1 >= 0 && iR < t.i1)) { t.d1 = d; t.i1 = iR; }
+                if (d < t.d1 || (d == t.d1 && t.i1 >= 0 && iR < t.i1)) { t.d1 = d; t.i1 = iR; bestX = uR; }
             }
         }
     }
-    // warp arg-min under (distance, iR)
+    // warp arg-min under (distance, iR); the winner's x travels with it
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const int od = __shfl_xor_sync(0xffffffffu, t.d1, o), oi = __shfl_xor_sync(0xffffffffu, t.i1, o);
-        if (lex_less(od, oi, t.d1, t.i1)) { t.d1 = od; t.i1 = oi; }
+        const float ox = __shfl_xor_sync(0xffffffffu, bestX, o);
+        if (lex_less(od, oi, t.d1, t.i1)) { t.d1 = od; t.i1 = oi; bestX = ox; }
     }
     if (t.i1 >= 0 && t.d1 < 75) { // thOrbDist = (TH_HIGH+TH_LOW)/2 (:582,663)
-        const float uR0 = SR.kps[t.i1].x;
+        const float uR0 = bestX;
         const float scaleFactor = P.isf[levelL];
         const float scaleduL = roundf(__fmul_rn(uL, scaleFactor)), scaledvL = roundf(__fmul_rn(vL, scaleFactor));
         const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
