@@ -42,7 +42,7 @@ for rep in sys.argv[2:]:
                 cols[key] = hit[0]
                 break
     for r in rows[2:]:
-        name = r[ik].split("(")[0].split("::")[-1]
+        name = r[ik].split("(")[0].split("::")[-1].replace("void ", "").split("<")[0].strip()
         ent = {"dram_bytes_per_launch": int(to_bytes(r[ir], units[ir]) + to_bytes(r[iw], units[iw])), "images_per_launch": imgs,
                "duration": r[it] + " " + units[it], "report": os.path.basename(rep)}
         for key, i in cols.items():
