@@ -96,7 +96,7 @@ __device__ __forceinline__ void cp_async16_zfill(void *smem, const void *gmem, b
 
 __device__ __forceinline__ void ds_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void ds_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-constexpr size_t DS_SMEM = 8 * 32 * 16 + (size_t)DS_WARPS * 2 * (DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
+constexpr size_t DS_SMEM = 8 * 32 * 16 + (size_t)DS_WARPS * (2 * DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
 
 __device__ __forceinline__ int dp4a_us(unsigned int a, unsigned int b, int c)
 {
@@ -124,12 +124,13 @@ template <int KW> __device__ __forceinline__ void disc_row_sums(const uint4 &q0,
     }
 }
 
-__global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __grid_constant__ ExtractParams P, int kpw)
+__global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __grid_constant__ ExtractParams P, int kpw)
 {
     extern __shared__ __align__(16) unsigned char ds_smem[];
     float4 *sPat = reinterpret_cast<float4 *>(ds_smem);                                // [bit k of the byte][lane]
-    // per warp, double buffered (this keypoint / the next one in flight): blurred patch, un-blurred patch
-    uint8_t *sPatchW = ds_smem + 8 * 32 * sizeof(float4) + (size_t)(threadIdx.x >> 5) * 2 * (DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
+    // per warp: blurred patch double buffered (this keypoint / the next one in flight); ONE un-blurred patch -- it is only read at the
+    // start of a keypoint (orientation), so the next keypoint's copy is issued right after that, under the descriptor computation
+    uint8_t *sPatchW = ds_smem + 8 * 32 * sizeof(float4) + (size_t)(threadIdx.x >> 5) * (2 * DS_PROWS * DS_PPITCH + DS_RROWS * DS_RPITCH);
     uint8_t *sRawW = sPatchW + 2 * DS_PROWS * DS_PPITCH;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         // pattern pair i belongs to descriptor byte i / 8 (= lane), bit i % 8
@@ -186,13 +187,10 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __gr
     };
     // blurred 37 x 37 patch (rows y-18..y+18, 16-byte chunks from (x-18) & ~15) and un-blurred 31 x 31 one (rows y-15..y+15 from
     // (x-15) & ~15, row 31 = zeros); chunks beyond the row pitch are zero-filled (src-size 0)
-    auto prefetch = [&](const Kp &k, uint8_t *patch, uint8_t *raw) {
+    auto prefetch_blur = [&](const Kp &k, uint8_t *patch) {
         const int gpitch = __shfl_sync(0xffffffffu, tPitch, k.l);
-        const unsigned int imgOff = __shfl_sync(0xffffffffu, tImgOff, k.l);
-        const uint8_t *bl = P.blur + (size_t)b * P.pyrStride + imgOff;
-        const uint8_t *img = k.l ? P.pyr + (size_t)b * P.pyrStride + imgOff : P.l0 + (size_t)b * P.l0ImgStride;
-        const int ipitch = k.l ? gpitch : P.l0Pitch;
-        const int px0 = (k.x - 18) & ~15, px1 = (k.x - 15) & ~15;
+        const uint8_t *bl = P.blur + (size_t)b * P.pyrStride + __shfl_sync(0xffffffffu, tImgOff, k.l);
+        const int px0 = (k.x - 18) & ~15;
 #pragma unroll
         for (int i = 0; i < 5; i++) {
             const int idx = lane + 32 * i; // chunk index: row = idx / 4, chunk = idx % 4
@@ -202,6 +200,13 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __gr
                 cp_async16_zfill(patch + r * DS_PPITCH + ((idx & 3) << 4), bl + (size_t)(k.y - 18 + r) * gpitch + (in ? gx : 0), in);
             }
         }
+    };
+    auto prefetch_raw = [&](const Kp &k, uint8_t *raw) {
+        const int gpitch = __shfl_sync(0xffffffffu, tPitch, k.l);
+        const unsigned int imgOff = __shfl_sync(0xffffffffu, tImgOff, k.l);
+        const uint8_t *img = k.l ? P.pyr + (size_t)b * P.pyrStride + imgOff : P.l0 + (size_t)b * P.l0ImgStride;
+        const int ipitch = k.l ? gpitch : P.l0Pitch;
+        const int px1 = (k.x - 15) & ~15;
 #pragma unroll
         for (int i = 0; i < 3; i++) {
             const int idx = lane + 32 * i; // row = idx / 3, chunk = idx % 3
@@ -209,22 +214,26 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __gr
             const bool in = idx < 31 * 3 && gx < ipitch;
             cp_async16_zfill(raw + idx * 16, img + (size_t)(k.y - 15 + (in ? r : 0)) * ipitch + (in ? gx : 0), in);
         }
-        ds_cp_commit();
     };
     const int slot0 = (blockIdx.x * DS_WARPS + wid) * kpw;
     Kp cur = decode(slot0);
-    if (cur.valid) prefetch(cur, sPatchW, sRawW);
+    if (cur.valid) { prefetch_blur(cur, sPatchW); prefetch_raw(cur, sRawW); ds_cp_commit(); }
     for (int kpi = 0; kpi < kpw; kpi++) {
         Kp nxt;
         nxt.valid = 0;
         if (kpi + 1 < kpw) nxt = decode(slot0 + kpi + 1);
-        // every lane is done with the buffer the next keypoint goes to (it held keypoint kpi - 1)
+        // every lane is done with the blurred buffer the next keypoint goes to (it held keypoint kpi - 1)
         __syncwarp();
-        if (nxt.valid) prefetch(nxt, sPatchW + ((kpi + 1) & 1) * DS_PROWS * DS_PPITCH, sRawW + ((kpi + 1) & 1) * DS_RROWS * DS_RPITCH);
-        if (!cur.valid) { cur = nxt; continue; }
+        if (nxt.valid) { prefetch_blur(nxt, sPatchW + ((kpi + 1) & 1) * DS_PROWS * DS_PPITCH); ds_cp_commit(); }
+        if (!cur.valid) {
+            if (nxt.valid) { prefetch_raw(nxt, sRawW); ds_cp_commit(); }
+            cur = nxt;
+            continue;
+        }
+        // outstanding groups, oldest first: blurred(cur), raw(cur) [, blurred(nxt)]
         if (nxt.valid) ds_cp_wait<1>(); else ds_cp_wait<0>();
         __syncwarp();
-        const uint8_t *patch = sPatchW + (kpi & 1) * DS_PROWS * DS_PPITCH, *raw = sRawW + (kpi & 1) * DS_RROWS * DS_RPITCH;
+        const uint8_t *patch = sPatchW + (kpi & 1) * DS_PROWS * DS_PPITCH, *raw = sRawW;
         const int l = cur.l, outIdx = cur.outIdx, x = cur.x, y = cur.y, resp = cur.resp;
         const int px0 = (x - 18) & ~15, px1 = (x - 15) & ~15;
 
@@ -233,6 +242,8 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 3) k_orient_describe(const __gr
         {
             const uint4 *rowp = reinterpret_cast<const uint4 *>(raw + lane * DS_RPITCH);
             const uint4 q0 = rowp[0], q1 = rowp[1], q2 = rowp[2];
+            __syncwarp(); // every lane holds its row: the un-blurred buffer is free for the next keypoint
+            if (nxt.valid) { prefetch_raw(nxt, sRawW); ds_cp_commit(); }
             const int o = (x - 15) - px1; // first disc column inside the staged row (warp-uniform)
             const unsigned int sb = (unsigned int)(o & 3) * 8u;
             int s, t;
