@@ -49,38 +49,27 @@ __device__ __forceinline__ unsigned int blur_load4(const uint8_t *row, int c, co
 
 #define BL_TAPS(a, b) ((unsigned int)(a) | ((unsigned int)(b) << 8))
 
-__global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ ExtractParams P)
+// rows [y0, yEnd) of one 120-column strip.  FASTROWS: rows up to yEnd+2 exist (no reflection inside the loop, the source row is a
+// running pointer); ALLINT: every lane loads an aligned word (no per-lane branch around the load)
+template <bool FASTROWS, bool ALLINT>
+__device__ __forceinline__ void blur_strip(const uint8_t *src, uint8_t *dst, int pitch, int dpitch, int y0, int yEnd, int H, int c,
+                                           const int (&cx)[4], bool interior, bool store)
 {
-    const int lane = threadIdx.x & 31;
-    const int item = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
-    if (item >= P.totalBlurTiles) return;
-    int l = 0;
-    while (l + 1 < P.nlevels && item >= P.geom[l + 1].blurTileBase) l++;
-    const LevelGeom g = P.geom[l];
-    const int b = blockIdx.y;
-    const int t = item - g.blurTileBase;
-    const int sx = t % g.blurTilesX, sy = t / g.blurTilesX;
-    const int W = g.w, H = g.h;
-    const int y0 = sy * BL_TH, yEnd = min(y0 + BL_TH, H);
-    const int c = sx * BL_TW - 4 + 4 * lane; // first of the lane's 4 virtual columns
-    int pitch, valid;
-    const uint8_t *src = level_ptr(P, g, l, b, pitch, valid);
-    uint8_t *dst = P.blur + (size_t)b * P.pyrStride + g.imgOff;
-    // lanes entirely beyond the reflected range never contribute (their neighbours' halo stays within +-3 of [0, W))
-    const bool interior = c >= 0 && c + 3 < W && ((((size_t)src) | (size_t)pitch) & 3) == 0;
-    const bool store = lane >= 1 && lane <= 30 && c < W;
-    int cx[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) cx[k] = (c + k < W + 3) ? reflect101(c + k, W) : 0; // columns past W + 2 feed no output
-
+    auto load_row = [&](int r) -> unsigned int { // the seven rows loaded before the loop may lie above the image also when FASTROWS
+        const uint8_t *row = src + (size_t)reflect_row(r, H) * pitch;
+        if (ALLINT) return __ldg(reinterpret_cast<const unsigned int *>(row + c));
+        return blur_load4(row, c, cx, interior);
+    };
     unsigned int ra[7], rb[7]; // ring of 7 rows, widened: ra = (p0, p1), rb = (p2, p3) in 16-bit lanes
 #pragma unroll
     for (int k = 0; k < 6; k++) {
-        const unsigned int w = blur_load4(src + (size_t)reflect_row(y0 - 3 + k, H) * pitch, c, cx, interior);
+        const unsigned int w = load_row(y0 - 3 + k);
         ra[k] = __byte_perm(w, 0u, 0x4140);
         rb[k] = __byte_perm(w, 0u, 0x4342);
     }
-    unsigned int nxt = blur_load4(src + (size_t)reflect_row(y0 + 3, H) * pitch, c, cx, interior);
+    unsigned int nxt = load_row(y0 + 3);
+    const uint8_t *nrow = src + (size_t)(y0 + 4) * pitch + c; // FASTROWS && ALLINT: the next source word, one pitch further per row
+    uint8_t *drow = dst + (size_t)y0 * dpitch + c;
     for (int base = y0; base < yEnd; base += 7) {
 #pragma unroll
         for (int k = 0; k < 7; k++) {
@@ -88,7 +77,11 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ Ex
             if (y < yEnd) { // warp-uniform
                 ra[(k + 6) % 7] = __byte_perm(nxt, 0u, 0x4140);
                 rb[(k + 6) % 7] = __byte_perm(nxt, 0u, 0x4342);
-                if (y + 1 < yEnd) nxt = blur_load4(src + (size_t)reflect_row(y + 4, H) * pitch, c, cx, interior);
+                if (y + 1 < yEnd) {
+                    if (FASTROWS && ALLINT) nxt = __ldg(reinterpret_cast<const unsigned int *>(nrow));
+                    else nxt = load_row(y + 4);
+                }
+                nrow += pitch;
                 // vertical pass: rows y-3 .. y+3 are ring slots k .. k+6 (mod 7)
                 const unsigned int Va = 18u * (ra[k % 7] + ra[(k + 6) % 7]) + 34u * (ra[(k + 1) % 7] + ra[(k + 5) % 7]) +
                                         48u * (ra[(k + 2) % 7] + ra[(k + 4) % 7]) + 56u * ra[(k + 3) % 7];
@@ -117,11 +110,45 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ Ex
                 if (store) {
                     const unsigned int lo = __byte_perm(o0, o1, 0x0062); // (o0 >> 16) | (o1 >> 16) << 8
                     const unsigned int hi = __byte_perm(o2, o3, 0x0062);
-                    *reinterpret_cast<unsigned int *>(dst + (size_t)y * g.pitch + c) = __byte_perm(lo, hi, 0x5410);
+                    *reinterpret_cast<unsigned int *>(drow) = __byte_perm(lo, hi, 0x5410);
                 }
+                drow += dpitch;
             }
         }
     }
+}
+
+__global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ ExtractParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const int item = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    if (item >= P.totalBlurTiles) return;
+    int l = 0;
+    while (l + 1 < P.nlevels && item >= P.geom[l + 1].blurTileBase) l++;
+    const LevelGeom g = P.geom[l];
+    const int b = blockIdx.y;
+    const int t = item - g.blurTileBase;
+    const int sx = t % g.blurTilesX, sy = t / g.blurTilesX;
+    const int W = g.w, H = g.h;
+    const int y0 = sy * BL_TH, yEnd = min(y0 + BL_TH, H);
+    const int c = sx * BL_TW - 4 + 4 * lane; // first of the lane's 4 virtual columns
+    int pitch, valid;
+    const uint8_t *src = level_ptr(P, g, l, b, pitch, valid);
+    uint8_t *dst = P.blur + (size_t)b * P.pyrStride + g.imgOff;
+    // lanes entirely beyond the reflected range never contribute (their neighbours' halo stays within +-3 of [0, W))
+    const bool interior = c >= 0 && c + 3 < W && ((((size_t)src) | (size_t)pitch) & 3) == 0;
+    const bool store = lane >= 1 && lane <= 30 && c < W;
+    int cx[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) cx[k] = (c + k < W + 3) ? reflect101(c + k, W) : 0; // columns past W + 2 feed no output
+
+    // two warp-uniform properties pick the loop variant: no row loaded inside the loop needs reflection (all but the last strip of a
+    // level) and no lane needs reflected columns (all but the strips at the left / right edge).  The generic loop spent 40 % of its
+    // instructions finding the word to load and the word to store.
+    const bool fastRows = yEnd + 3 <= H;
+    const bool allInt = __all_sync(0xffffffffu, interior);
+    if (fastRows && allInt) blur_strip<true, true>(src, dst, pitch, g.pitch, y0, yEnd, H, c, cx, interior, store);
+    else blur_strip<false, false>(src, dst, pitch, g.pitch, y0, yEnd, H, c, cx, interior, store);
 }
 
 #endif // ORBB200_EXTRACT_IMPL
