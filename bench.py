@@ -236,7 +236,7 @@ def run_reference(args, rank, world):
     P = args.pairs
     have_ref = R.available()
     nthreads = max(1, cores // 2) if have_ref else cores  # the stereo constructor runs two extraction threads per session
-    npairs = min(P, max(nthreads, 4) * 2)                # bounded sample of the step's P pairs
+    npairs = min(P, max(nthreads, 4) * 8)                # bounded sample of the step's P pairs (about 0.5 s wall per step)
     imgs = make_pairs(P)[:2 * npairs]
     fn = cpu_reference_pairs if have_ref else cpu_extract_pairs
     for _ in range(max(1, min(args.warmup, 2))):
@@ -483,7 +483,7 @@ def run_b200(args, rank, world, local_rank):
         cores = os.cpu_count() or 1
         have_ref = orbslam_ref.available()
         nthreads = max(1, cores // 2) if have_ref else cores
-        sample_pairs = min(P, max(nthreads, 4) * 4)  # ~10-20 s of CPU work spread over all cores
+        sample_pairs = min(P, max(nthreads, 4) * 16)  # ~15-20 s of CPU work spread over all cores (about 1.2 s wall on 16 cores)
         fn = cpu_reference_pairs if have_ref else cpu_extract_pairs
         dt, nimg = fn(host_imgs.numpy()[:2 * sample_pairs], nthreads)
         line["cpu_baseline"] = {"value": nimg / dt, "unit": "frames/s", "cores": cores, "kind": "reference" if have_ref else "port",
