@@ -8,6 +8,10 @@
 struct orbb200_extractor {
     int device = 0;
     cudaStream_t stream = nullptr;
+    // single frames / pairs: the blur of the pyramid runs on sideStream beside FAST + quadtree (fork after the last resize, join
+    // before the descriptor stage); batches keep one stream (both sides are issue bound there)
+    cudaStream_t sideStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
     // E1 tables (src/ORBextractor.cc:429-534)
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
     double scaleFactor = 0;
