@@ -245,26 +245,17 @@ template <int MAXT> __device__ bool octree_fast(const ExtractParams &P, const Le
                     skeys[nvis + ex] = ((unsigned long long)cCnt[p] << 40) | ((unsigned long long)(cSeq[p] & 0xFFFFF) << 20) | (unsigned long long)p;
                 nvis += tot;
             }
-            int S = 1;
-            while (S < nvis) S <<= 1;
-            for (int i = nvis + tid; i < S; i += NT) skeys[i] = 0ull;
             __syncthreads();
-            for (int k = 2; k <= S; k <<= 1)
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < S; i += NT) {
-                        const int ixj = i ^ j;
-                        if (ixj > i) {
-                            const unsigned long long a = skeys[i], c = skeys[ixj];
-                            const bool desc = (i & k) == 0;
-                            if (desc ? a < c : a > c) { skeys[i] = c; skeys[ixj] = a; }
-                        }
-                    }
-                    __syncthreads();
-                }
+            // order by rank counting: keys are unique (they end in the list position), so the rank of a key = the number of larger
+            // keys; every thread reads the whole key array (broadcast reads, no barrier inside) -- for the few hundred nodes of a
+            // level this beats a bitonic network's log^2 barrier rounds
             for (int r = tid; r < nvis; r += NT) {
-                const int p = (int)(skeys[r] & 0xFFFFFull);
-                vis[r] = p;
-                vrank[p] = r;
+                const unsigned long long key = skeys[r];
+                int rank = 0;
+                for (int j = 0; j < nvis; j++) rank += skeys[j] > key ? 1 : 0;
+                const int p = (int)(key & 0xFFFFFull);
+                vis[rank] = p;
+                vrank[p] = rank;
             }
         }
         if (tid == 0) { ctl->nexp = 0; ctl->rstar = nvis - 1; ctl->ovf = 0x7fffffff; }
