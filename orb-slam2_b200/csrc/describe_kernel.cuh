@@ -265,16 +265,21 @@ __global__ void __launch_bounds__(DS_WARPS * 32, 4) k_orient_describe(const __gr
         double sd, cd;
         sincos_0_2pi((double)ang, &sd, &cd);
         const float a = (float)cd, bsn = (float)sd;
-        const uint8_t *pc = patch + 18 * DS_PPITCH + (x - px0); // patch centre
+        // cvRound by the magic-number add leaves K + n in the float's bits (K = 0x4B400000); instead of subtracting K from every row
+        // and column, the patch-centre address carries -(DS_PPITCH + 1) * K once (32-bit shared-window arithmetic, wraps exactly)
+        static_assert(DS_PPITCH == 64, "the row stride is applied as a shift");
+        const unsigned int pcK = (unsigned int)__cvta_generic_to_shared(patch + 18 * DS_PPITCH + (x - px0)) - 65u * 0x4B400000u;
+        auto round_bits = [](float v) { return (unsigned int)__float_as_int(__fadd_rn(v, 12582912.0f)); }; // |v| < 2^22
+        auto lds_u8 = [](unsigned int addr) { unsigned int r; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(addr)); return r; };
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const float4 p = sPat[k * 32 + lane];
-            const int r0 = cv_round_magic(__fadd_rn(__fmul_rn(p.x, bsn), __fmul_rn(p.y, a)));
-            const int c0 = cv_round_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, bsn)));
-            const int r1 = cv_round_magic(__fadd_rn(__fmul_rn(p.z, bsn), __fmul_rn(p.w, a)));
-            const int c1 = cv_round_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, bsn)));
-            const int t0 = pc[r0 * DS_PPITCH + c0], t1 = pc[r1 * DS_PPITCH + c1];
+            const unsigned int r0 = round_bits(__fadd_rn(__fmul_rn(p.x, bsn), __fmul_rn(p.y, a)));
+            const unsigned int c0 = round_bits(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, bsn)));
+            const unsigned int r1 = round_bits(__fadd_rn(__fmul_rn(p.z, bsn), __fmul_rn(p.w, a)));
+            const unsigned int c1 = round_bits(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, bsn)));
+            const unsigned int t0 = lds_u8(pcK + (r0 << 6) + c0), t1 = lds_u8(pcK + (r1 << 6) + c1);
             val |= (t0 < t1) << k;
         }
         P.desc[((size_t)b * P.cap + outIdx) * 32 + lane] = (uint8_t)val;
