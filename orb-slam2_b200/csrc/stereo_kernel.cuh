@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(512) k_stereo_rows(const __grid_constant__ Ste
     }
 }
 
-__global__ void __launch_bounds__(256) k_stereo_match(const __grid_constant__ StereoParams P)
+__global__ void __launch_bounds__(256, 8) k_stereo_match(const __grid_constant__ StereoParams P)
 {
     const int lane = threadIdx.x & 31;
     const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;

@@ -54,7 +54,7 @@ for _ in range(5):
 torch.cuda.synchronize()
 print("D2H %d MB: %.2f ms" % (dk.numel() >> 20, (time.perf_counter() - t0) / 5 * 1e3))
 ref = None
-for chunk, ns in [(16, 8), (8, 8), (10, 8), (12, 8), (20, 8), (16, 4), (16, 12), (32, 8), (16, 8)]:
+for chunk, ns in [(16, 8), (8, 8), (12, 8), (20, 8), (24, 8), (32, 8), (16, 4), (16, 6), (32, 4), (16, 8)]:
     ex.set_pipeline(chunk, ns)
     ms = run()
     cs = int(n_h.numpy().astype(np.int64).sum()) * 1000003 + int(desc_h.numpy()[:, :100].astype(np.int64).sum())
