@@ -20,6 +20,10 @@ namespace orbb200 {
 
 constexpr int BL_TW = 120, BL_TH = 64; // outputs per warp strip (columns) and rows per work item
 constexpr int BL_WARPS = 4, BL_THREADS = BL_WARPS * 32;
+#ifndef ORBB200_BL_MINBLOCKS
+#define ORBB200_BL_MINBLOCKS 12
+#endif
+constexpr int BL_MINBLOCKS = ORBB200_BL_MINBLOCKS;
 
 #ifdef ORBB200_EXTRACT_IMPL
 
@@ -118,7 +122,7 @@ __device__ __forceinline__ void blur_strip(const uint8_t *src, uint8_t *dst, int
     }
 }
 
-__global__ void __launch_bounds__(BL_THREADS) k_blur7(const __grid_constant__ ExtractParams P)
+__global__ void __launch_bounds__(BL_THREADS, BL_MINBLOCKS) k_blur7(const __grid_constant__ ExtractParams P)
 {
     const int lane = threadIdx.x & 31;
     const int item = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);

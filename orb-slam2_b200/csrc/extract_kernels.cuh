@@ -128,7 +128,7 @@ __device__ __forceinline__ unsigned int prmt_dyn(unsigned int a, unsigned int b,
     return r;
 }
 
-__global__ void __launch_bounds__(RZ_THREADS) k_pyramid_resize(const __grid_constant__ ExtractParams P, int l)
+__global__ void __launch_bounds__(RZ_THREADS, 8) k_pyramid_resize(const __grid_constant__ ExtractParams P, int l)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const LevelGeom g = P.geom[l], gs = P.geom[l - 1];
