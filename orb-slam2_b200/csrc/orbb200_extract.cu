@@ -55,7 +55,7 @@ static int opt_in_shared_memory(int device)
     ORB_CUDA_OK(cudaFuncSetAttribute(k_pyramid_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
-    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     ORB_CUDA_OK(cudaFuncSetAttribute(k_octree_select<OCT_THREADS_BIG, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
     done[device] = true;
     return ORBB200_OK;
@@ -113,11 +113,12 @@ int extractor_ensure_shape(orbb200_extractor *e, int w, int h, int batch)
             g.nodeWsOff = (unsigned int)wsOff;
             wsOff += align_up((size_t)21 * g.nodeCap, 32);
             octSmem = std::max(octSmem, align_up((size_t)44 * g.nodeCap, 16) + (size_t)8 * g.sortLen);
-            // histogram formulation: the deepest table that fits the block's shared-memory budget (3 blocks of 256 threads per SM;
-            // one block of 1024 threads per SM for images above 1 Mpixel)
+            // histogram formulation: the deepest table that fits the block's shared-memory budget (6 blocks of 256 threads per SM --
+            // the node passes are barrier / latency bound, so blocks per SM count for more than table depth: 0.31 ms at 3 blocks and
+            // depth 6, 0.24 ms at 6 blocks and depth 5 per 320 KITTI images; one block of 1024 threads per SM for images above 1 Mpixel)
             g.octDepth = 0;
             if (width > 0 && height > 0 && g.nodeCap < 65535 && nIni <= 255) {
-                const size_t budget = bigImage ? (size_t)196 * 1024 : (size_t)72 * 1024;
+                const size_t budget = bigImage ? (size_t)196 * 1024 : (size_t)36 * 1024;
                 for (int D = OCT_MAX_DEPTH; D >= 3; D--)
                     if (oct_fast_smem(nIni, D, g.nodeCap, g.sortLen, (int)width, (int)height) <= budget) { g.octDepth = D; break; }
                 if (g.octDepth) octSmem = std::max(octSmem, oct_fast_smem(nIni, g.octDepth, g.nodeCap, g.sortLen, (int)width, (int)height));
