@@ -377,6 +377,8 @@ def run_b200(args, rank, world, local_rank):
             issue = {k: ent[k] for k in ("issue_slots_busy_pct", "sm_throughput_pct", "alu_pipe_pct", "l1tex_throughput_pct",
                                          "lsu_shared_wavefronts_pct", "dram_throughput_pct", "warp_instructions", "ipc_active",
                                          "registers_per_thread", "achieved_occupancy_pct") if k in ent}
+            if "ipc_active" in issue:
+                issue["frac"] = issue["ipc_active"] / 4.0  # achieved warp-instructions per clock per SM over the 4 an SM can issue
             issue["source"] = "profiles/" + str(ent.get("report", "r2_traffic.json")) + " via profiles/r2_traffic.json (ncu --set full, one launch)"
     except Exception:
         pass

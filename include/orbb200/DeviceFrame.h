@@ -13,6 +13,8 @@
  *                            mfGridElementWidthInv, mfGridElementHeightInv)
  *   WindowSearch(...)        grid build + GetFeaturesInArea + all distances of a windowed search against this frame:
  *                            only the windows and the query descriptors travel (orbb200_window_search_resident)
+ *   ComputeBoW(voc, v, fv)   Frame::ComputeBoW (:459-466) on the resident descriptors (orbb200_compute_bow_batch_device): only the
+ *                            BowVector / FeatureVector come back
  *   Keys() / KeysUn() / Descriptors()   host copies, materialised on first read
  *
  * ORBmatcher's windowed searches take this path by themselves when the caller's Frame type has a member
@@ -113,6 +115,45 @@ public:
         return fail();
     }
 
+    /* Frame::ComputeBoW on the resident descriptors: voc.transform(mDescriptors, v, fv, 4) without the descriptors leaving the device.
+     * Voc = orbb200::ORBVocabulary (anything with handle()), BowVec / FeatVec = DBoW2::BowVector / FeatureVector (std::map based). */
+    template <class Voc, class BowVec, class FeatVec> bool ComputeBoW(const Voc &voc, BowVec &v, FeatVec &fv, int levelsup = 4)
+    {
+        v.clear();
+        fv.clear();
+        if (n_ == 0 || !voc.handle()) return true;
+        if (capN_ > 8192) { std::cerr << "DeviceFrame::ComputeBoW: more than 8192 keypoint slots" << std::endl; return false; }
+        if (!bow_d_) {
+            // one block: n, n_bow, n_kept (ints, 64 bytes) | bow_id [cap] | bow_val [cap] doubles | fv_key [cap] u64
+            const size_t bytes = 64 + (size_t)capN_ * (4 + 8 + 8) + 64;
+            if (orbb200_device_alloc((void **)&bow_d_, bytes, device_) != ORBB200_OK) return fail();
+            bowCap_ = capN_;
+        }
+        unsigned char *base = bow_d_;
+        int *cnt_d = reinterpret_cast<int *>(base);
+        double *val_d = reinterpret_cast<double *>(base + 64);
+        unsigned long long *key_d = reinterpret_cast<unsigned long long *>(base + 64 + (size_t)bowCap_ * 8);
+        int *id_d = reinterpret_cast<int *>(base + 64 + (size_t)bowCap_ * 16);
+        if (orbb200_copy_to_device(cnt_d, &n_, sizeof(int)) != ORBB200_OK) return fail();
+        if (orbb200_compute_bow_batch_device(voc.handle(), desc_d_, cnt_d, 1, bowCap_, levelsup, id_d, val_d, cnt_d + 1, key_d, cnt_d + 2, nullptr) !=
+            ORBB200_OK)
+            return fail();
+        if (orbb200_device_sync(device_) != ORBB200_OK) return fail();
+        int cnt[3];
+        if (orbb200_copy_to_host(cnt, cnt_d, sizeof(cnt)) != ORBB200_OK) return fail();
+        std::vector<int> ids(cnt[1] + 1);
+        std::vector<double> vals(cnt[1] + 1);
+        std::vector<unsigned long long> keys(cnt[2] + 1);
+        if (cnt[1] && (orbb200_copy_to_host(ids.data(), id_d, sizeof(int) * (size_t)cnt[1]) != ORBB200_OK ||
+                       orbb200_copy_to_host(vals.data(), val_d, sizeof(double) * (size_t)cnt[1]) != ORBB200_OK))
+            return fail();
+        if (cnt[2] && orbb200_copy_to_host(keys.data(), key_d, sizeof(unsigned long long) * (size_t)cnt[2]) != ORBB200_OK) return fail();
+        for (int j = 0; j < cnt[1]; j++) v.insert(v.end(), typename BowVec::value_type((typename BowVec::key_type)ids[j], vals[j]));
+        for (int j = 0; j < cnt[2]; j++) // keys ascend: node groups in map order, feature indices ascending inside a group
+            fv[(typename FeatVec::key_type)(keys[j] >> 32)].push_back((unsigned int)(keys[j] & 0xFFFFFFFFull));
+        return true;
+    }
+
     /* host views, downloaded on first read */
     const std::vector<cv::KeyPoint> &Keys()
     {
@@ -151,6 +192,8 @@ private:
         orbb200_device_free(kps_d_);
         orbb200_device_free(kpsUn_d_);
         orbb200_device_free(desc_d_);
+        orbb200_device_free(bow_d_);
+        bow_d_ = nullptr;
         kps_d_ = kpsUn_d_ = nullptr;
         desc_d_ = nullptr;
         capN_ = 0;
@@ -174,6 +217,8 @@ private:
 
     orbb200_keypoint *kps_d_, *kpsUn_d_;
     uint8_t *desc_d_;
+    unsigned char *bow_d_ = nullptr; // ComputeBoW's device block (allocated on first use)
+    int bowCap_ = 0;
     int n_, capN_, device_;
     float minX_, minY_, invW_, invH_;
     int cols_, rows_;

@@ -11,6 +11,7 @@
 
 #include "orbb200/ORBextractor.h"
 #include "orbb200/ORBmatcher.h"
+#include "orbb200/ORBVocabulary.h"
 
 static unsigned long long g_s = 88172645463325252ull;
 static unsigned rnd() { g_s ^= g_s << 13; g_s ^= g_s >> 7; g_s ^= g_s << 17; return (unsigned)(g_s >> 11); }
@@ -114,6 +115,39 @@ int main(int argc, char **argv)
     printf("h2d bytes: host frame %llu, device frame %llu (frame itself: %llu)\n", hostBytes, devBytes, (unsigned long long)F.N * 60ull);
     fails += check(hostBytes == devBytes + (unsigned long long)F.N * 60ull && devBytes % 52 == 0 && devBytes > 0,
                    "the device-resident search uploads windows + query descriptors only (52 bytes per query, nothing of the frame)");
+    // Frame::ComputeBoW (src/Frame.cc:459-466) on the resident descriptors == the host-buffer transform of the same vocabulary
+    {
+        const int k = 6, L = 3; // complete tree: 1 + 6 + 36 + 216 nodes, words = the 216 leaves
+        std::vector<int> parent(1, -1);
+        std::vector<unsigned char> leaf(1, 0);
+        std::vector<int> level(1, 0);
+        for (size_t n = 0; n < parent.size(); n++)
+            if (level[n] < L)
+                for (int c = 0; c < k; c++) { parent.push_back((int)n); level.push_back(level[n] + 1); leaf.push_back(level[n] + 1 == L); }
+        const int nn = (int)parent.size();
+        std::vector<unsigned char> vdesc((size_t)nn * 32);
+        std::vector<double> w(nn, 0.0);
+        for (int n = 1; n < nn; n++) {
+            memcpy(&vdesc[(size_t)n * 32], F.mDescriptors.ptr((int)(rnd() % F.N)), 32); // centres near real descriptors
+            for (int j = 0; j < 20; j++) { const unsigned bit = rnd() % 256; vdesc[(size_t)n * 32 + (bit >> 3)] ^= (unsigned char)(1u << (bit & 7)); }
+            w[n] = leaf[n] ? 0.25 + rndf() * 3.0 : 0.0;
+        }
+        parent[0] = 0;
+        orbb200::ORBVocabulary voc;
+        voc.create(k, L, 0 /* L1 */, 0 /* TF_IDF */, nn, parent.data(), leaf.data(), vdesc.data(), w.data());
+        DBoW2::BowVector v1, v2;
+        DBoW2::FeatureVector f1, f2;
+        voc.transform(F.mDescriptors, v1, f1, 2);
+        const unsigned long long c0 = orbb200_h2d_bytes_total();
+        const bool okBow = dev.ComputeBoW(voc, v2, f2, 2);
+        const unsigned long long c1 = orbb200_h2d_bytes_total();
+        bool sameBow = okBow && v1.size() == v2.size() && f1.size() == f2.size() && v1.size() > 50 && f1.size() > 3;
+        for (DBoW2::BowVector::const_iterator a = v1.begin(), b2 = v2.begin(); sameBow && a != v1.end(); ++a, ++b2)
+            sameBow = a->first == b2->first && a->second == b2->second;
+        for (DBoW2::FeatureVector::const_iterator a = f1.begin(), b2 = f2.begin(); sameBow && a != f1.end(); ++a, ++b2)
+            sameBow = a->first == b2->first && a->second == b2->second;
+        fails += check(sameBow && c1 - c0 <= 16, "ComputeBoW on the resident descriptors == the host-buffer transform (words, values, feature lists); nothing uploaded");
+    }
     printf("%s: %d check(s) failed\n", fails ? "FAIL" : "ok", fails);
     return fails ? 1 : 0;
 }

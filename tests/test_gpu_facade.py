@@ -101,7 +101,7 @@ def test_device_resident_frame_searches_without_reupload(tmp_path):
     p = str(tmp_path / "img.raw")
     img.tofile(p)
     r = subprocess.run([exe, "640", "480", p], capture_output=True, text=True, timeout=120)
-    assert r.returncode == 0 and r.stdout.count("ok ") == 5 and "FAIL" not in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and r.stdout.count("ok ") == 6 and "FAIL" not in r.stdout, r.stdout + r.stderr
 
 
 def test_facade_matcher_equals_compiled_reference_on_reference_types():
