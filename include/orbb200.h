@@ -344,6 +344,24 @@ int orbb200_extract_stereo_batch(orbb200_extractor *e, const uint8_t *const *img
                                  int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out, float bf, float b,
                                  float *uRight, float *depth, int *n_valid);
 
+/* begin / wait form of the two host-buffer batch calls, for callers that stream a sequence through one handle (a dataset
+ * replay, a serving loop): *_begin submits the whole pipelined call and returns at once with a ticket; orbb200_extract_batch_wait
+ * blocks until that call's results are in its host buffers (and reports ORBB200_ERR_CAPACITY like the synchronous call).  Up to
+ * TWO calls may be in flight on a handle, so the input copies of call k + 1 run under the last kernels and downloads of call k
+ * (a synchronous call pays its first copy and its last chunk's kernels as pure latency, and keeps its chunks small to keep them
+ * short; begun calls use 64-image chunks: on one B200 the step of 160 KITTI pairs takes 4.4 ms synchronously and 3.6 ms streamed,
+ * against 3.5 ms of kernel time with everything resident).  Rules: the host buffers of a begun call (inputs
+ * and outputs) must not be touched until its wait; consecutive begun calls need different output buffers; a third begin first
+ * completes the oldest call; calls of a different shape / batch / capacity complete the calls in flight before they start; any
+ * other entry point taking the handle (orbb200_extract, *_device, orbb200_extractor_sync, destroy) completes them too.  The
+ * synchronous calls are begin + wait.  (No counterpart in the reference, whose Frame constructor is synchronous.) */
+int orbb200_extract_batch_begin(orbb200_extractor *e, const uint8_t *const *imgs, int batch, int width, int height, int stride,
+                                orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out, int *ticket);
+int orbb200_extract_stereo_batch_begin(orbb200_extractor *e, const uint8_t *const *imgs, int npairs, int width, int height,
+                                       int stride, orbb200_keypoint *kps, uint8_t *desc, int cap, int *n_out, float bf, float b,
+                                       float *uRight, float *depth, int *n_valid, int *ticket);
+int orbb200_extract_batch_wait(orbb200_extractor *e, int ticket);
+
 /* ---- DBoW2 vocabulary transform (Frame::ComputeBoW, src/Frame.cc:459-466; KeyFrame::ComputeBoW, src/KeyFrame.cc:59-69) ----
  * ORBVocabulary = DBoW2::TemplatedVocabulary<cv::Mat, FORB> (include/ORBVocabulary.h:31-32); file:line below are under
  * Thirdparty/DBoW2/DBoW2/.  scoring / weighting use the reference's enum values (BowVector.h:36-53):

@@ -54,9 +54,21 @@ struct orbb200_extractor {
     static constexpr int PIPE_STAGES = 6; // staging buffers: the H2D copies run up to 6 chunks ahead of the stage kernels
     cudaEvent_t evH2D[PIPE_STAGES] = {}, evDone[PIPE_STAGES] = {}, evStaged[PIPE_STAGES] = {};
     cudaEvent_t evWork[PIPE_STREAMS] = {}, evBegin = nullptr;
+    // begin / wait form of the host-buffer batch calls: up to two calls in flight on a handle, so that the copies of call k + 1 run
+    // under the tail of call k.  evChunkOut[ci]: the download of chunk ci of the previous call is complete (its device output block
+    // may be overwritten by chunk ci of the next call)
+    struct PendingCall { bool active = false; int batch = 0, cap = 0, chunk = 0, width = 0, height = 0, stereo = 0; int *n_out = nullptr; cudaEvent_t done = nullptr; };
+    PendingCall pend[2];
+    int pendNext = 0;
+    std::vector<cudaEvent_t> evChunkOut;
+    size_t chunkOutRecorded = 0;
     uint8_t *d_stage[PIPE_STAGES] = {};
     size_t stageBytes = 0;
     int pipeChunk = 16, pipeStreams = 8, devChunk = 0;
+    // begun (streamed) calls have no head / tail to keep short, so they take larger chunks, whose kernels fill the GPU better:
+    // 160 KITTI pairs per step, two steps in flight: 4.02 ms at 16 images per chunk, 3.60 ms at 64.  orbb200_extractor_set_pipeline
+    // fixes the chunk size for both forms.
+    int pipeChunkStreamed = 64;
     // single-image latency path (orbb200_extract): pinned bounce buffers + the whole launch sequence (H2D, level-0 staging,
     // pyramid, FAST, quadtree, blur, describe, D2H) captured once per (shape, capacity) in a CUDA graph
     uint8_t *h_in = nullptr, *h_out = nullptr, *d_in1 = nullptr;

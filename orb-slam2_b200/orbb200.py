@@ -17,7 +17,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
 
 EXPORTS = [
-    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity", "orbb200_pyramid_layout", "orbb200_pyramid_download", "orbb200_pyramid_map", "orbb200_host_alloc", "orbb200_host_free", "orbb200_window_search_resident", "orbb200_extractor_outputs_device", "orbb200_device_alloc", "orbb200_device_free", "orbb200_copy_to_device", "orbb200_copy_to_host", "orbb200_copy_on_device", "orbb200_h2d_bytes_total", "orbb200_device_sync", "orbb200_bind_host_to_device", "orbb200_extractor_set_graph", "orbb200_extractor_set_octree_depth",
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity", "orbb200_pyramid_layout", "orbb200_pyramid_download", "orbb200_pyramid_map", "orbb200_host_alloc", "orbb200_host_free", "orbb200_window_search_resident", "orbb200_extractor_outputs_device", "orbb200_device_alloc", "orbb200_device_free", "orbb200_copy_to_device", "orbb200_copy_to_host", "orbb200_copy_on_device", "orbb200_h2d_bytes_total", "orbb200_device_sync", "orbb200_bind_host_to_device", "orbb200_extractor_set_graph", "orbb200_extractor_set_octree_depth", "orbb200_extract_batch_begin", "orbb200_extract_stereo_batch_begin", "orbb200_extract_batch_wait",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
@@ -63,6 +63,9 @@ def lib():
     L.orbb200_pyramid_download.argtypes = [vp, ip, vp, sz]
     L.orbb200_pyramid_map.argtypes = [vp, ip, vp]
     L.orbb200_extractor_set_octree_depth.argtypes = [vp, ip]
+    L.orbb200_extract_batch_begin.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, vp]
+    L.orbb200_extract_stereo_batch_begin.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, fp, fp, vp, vp, vp, vp]
+    L.orbb200_extract_batch_wait.argtypes = [vp, ip]
     L.orbb200_extractor_set_graph.argtypes = [vp, ip]
     L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]

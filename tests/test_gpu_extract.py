@@ -268,3 +268,61 @@ def test_quadtree_formulations_agree(configs, name):
     for b, im in enumerate((img, clustered, img)):
         kc, dc = ref.extract(im)
         _compare(kps[b, :n[b]], desc[b, :n[b]], kc, dc)
+
+
+def test_begin_wait_stream_of_stereo_batches_equals_synchronous_calls(configs):
+    """orbb200_extract_stereo_batch_begin / orbb200_extract_batch_wait: a stream of steps with two calls in flight on one handle (the
+    copies of step k + 1 under the tail of step k, device output blocks and staging buffers reused) gives, step by step, the results
+    of the synchronous call -- also when a call of another size comes in between and when a third begin arrives before a wait."""
+    import ctypes as C
+    w, h, nf, sfac, nl, ini, mn = configs["kitti"]
+    L = orbb200.lib()
+    ex = orbb200.ORBextractor(nf, sfac, nl, ini, mn)
+    ex.set_pipeline(4, 8)  # several chunks per call at this small size
+    cap = ex.cap
+    bf, b = 386.1448, 386.1448 / 718.856
+    steps = []
+    for s in range(5):
+        npairs = 7 if s != 3 else 3  # step 3 has another size: the calls in flight are completed first
+        imgs = np.ascontiguousarray(np.stack([v for p in range(npairs) for v in synth.stereo_pair(w, h, 100 * s + p)]))
+        steps.append((npairs, imgs))
+
+    def buffers(npairs):
+        return dict(kps=np.zeros((2 * npairs, cap), orbb200.KP_DTYPE), desc=np.zeros((2 * npairs, cap, 32), np.uint8), n=np.zeros(2 * npairs, np.int32),
+                    uR=np.zeros((npairs, cap), np.float32), dep=np.zeros((npairs, cap), np.float32), nv=np.zeros(npairs, np.int32))
+
+    def ptrs(imgs):
+        return (C.c_void_p * len(imgs))(*[imgs[i].ctypes.data for i in range(len(imgs))])
+
+    want = []
+    for npairs, imgs in steps:
+        o = buffers(npairs)
+        orbb200.check(L.orbb200_extract_stereo_batch(ex.h, ptrs(imgs), npairs, w, h, w, orbb200._p(o["kps"]), orbb200._p(o["desc"]), cap, orbb200._p(o["n"]),
+                                                     bf, b, orbb200._p(o["uR"]), orbb200._p(o["dep"]), orbb200._p(o["nv"])))
+        want.append(o)
+    got, tickets, keep = [], [], []
+    for npairs, imgs in steps:  # begin all five back to back: never more than two in flight, the third begin completes the oldest
+        o = buffers(npairs)
+        t = C.c_int(-5)
+        pp = ptrs(imgs)
+        keep.append(pp)
+        orbb200.check(L.orbb200_extract_stereo_batch_begin(ex.h, pp, npairs, w, h, w, orbb200._p(o["kps"]), orbb200._p(o["desc"]), cap, orbb200._p(o["n"]),
+                                                           bf, b, orbb200._p(o["uR"]), orbb200._p(o["dep"]), orbb200._p(o["nv"]), C.byref(t)))
+        assert t.value in (0, 1)
+        got.append(o)
+        tickets.append(t.value)
+    for t in tickets[-2:]:
+        orbb200.check(L.orbb200_extract_batch_wait(ex.h, t))
+    orbb200.check(L.orbb200_extract_batch_wait(ex.h, tickets[0]))  # already complete: a no-op
+    for s, (a, g) in enumerate(zip(want, got)):
+        assert np.array_equal(a["n"], g["n"]) and a["n"].min() > 500, s
+        assert np.array_equal(a["nv"], g["nv"]) and a["nv"].min() > 100, s
+        for i in range(len(a["n"])):
+            k = a["n"][i]
+            assert np.array_equal(a["kps"][i, :k], g["kps"][i, :k]) and np.array_equal(a["desc"][i, :k], g["desc"][i, :k]), (s, i)
+        for p in range(len(a["nv"])):
+            k = a["n"][2 * p]
+            assert np.array_equal(a["uR"][p, :k], g["uR"][p, :k]) and np.array_equal(a["dep"][p, :k], g["dep"][p, :k]), (s, p)
+    # the handle is back in its synchronous state: a single-image call right after
+    k1, d1 = ex(steps[0][1][0])
+    assert np.array_equal(k1, want[0]["kps"][0, :want[0]["n"][0]])
