@@ -57,7 +57,8 @@ struct orbb200_extractor {
     // begin / wait form of the host-buffer batch calls: up to two calls in flight on a handle, so that the copies of call k + 1 run
     // under the tail of call k.  evChunkOut[ci]: the download of chunk ci of the previous call is complete (its device output block
     // may be overwritten by chunk ci of the next call)
-    struct PendingCall { bool active = false; int batch = 0, cap = 0, chunk = 0, width = 0, height = 0, stereo = 0; int *n_out = nullptr; cudaEvent_t done = nullptr; };
+    struct PendingCall { bool active = false; int batch = 0, cap = 0, chunk = 0, width = 0, height = 0, stereo = 0; int *n_out = nullptr; cudaEvent_t done = nullptr;
+                         int result = 0; bool unreported = false; }; // result of a call completed by a later begin, kept for its wait
     PendingCall pend[2];
     int pendNext = 0;
     std::vector<cudaEvent_t> evChunkOut;
