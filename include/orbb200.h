@@ -419,6 +419,27 @@ int orbb200_compute_bow_batch_device(orbb200_vocabulary *v, const uint8_t *desc_
                                      int levelsup, int *bow_id_d, double *bow_val_d, int *n_bow_d,
                                      unsigned long long *fv_key_d, int *n_kept_d, void *stream);
 
+/* ---- EuRoC prologue: stereo rectification (Examples/Stereo/stereo_euroc.cc:60-97, 131-132) ----
+ * The example rectifies both images of every frame with cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) before TrackStereo, M1 / M2
+ * from cv::initUndistortRectifyMap(K, D, R, P.rowRange(0,3).colRange(0,3), size, CV_32F, M1, M2) once per run. */
+typedef struct orbb200_remap orbb200_remap; /* opaque: one (M1, M2) pair converted to OpenCV's fixed-point form, resident in HBM */
+/* map_x / map_y: host [dst_height][dst_width] float (CV_32FC1 maps as initUndistortRectifyMap writes them) */
+int orbb200_remap_create(orbb200_remap **out, const float *map_x, const float *map_y, int dst_width, int dst_height, int device);
+void orbb200_remap_destroy(orbb200_remap *r);
+/* replaces cv::remap(src, dst, M1, M2, cv::INTER_LINEAR) (BORDER_CONSTANT, value 0) for `batch` 8-bit one-channel images of one shape,
+ * bit-exact with OpenCV's fixed-point path (5 fraction bits, 15-bit weights).  Host images in, host images out: */
+int orbb200_remap_batch(orbb200_remap *r, const uint8_t *const *imgs, int batch, int src_width, int src_height, int src_stride,
+                        uint8_t *const *out, int out_stride);
+/* the same on device memory, asynchronous on `stream` (a cudaStream_t; NULL = the handle's own): image b at imgs_d + b *
+ * src_image_stride, result b at out_d + b * out_image_stride -- chains in front of orbb200_extract_batch_device without a host
+ * round trip */
+int orbb200_remap_batch_device(orbb200_remap *r, const uint8_t *imgs_d, int batch, int src_width, int src_height, int src_stride,
+                               size_t src_image_stride, uint8_t *out_d, int out_stride, size_t out_image_stride, void *stream);
+/* replaces cv::initUndistortRectifyMap(K, D, R, P(3x3), (width, height), CV_32F, map_x, map_y): K, R, P row-major 3x3 doubles, D =
+ * (k1, k2, p1, p2, k3) with n_dist <= 5 entries given.  Host arithmetic (runs once per sequence, needs no device). */
+int orbb200_init_undistort_rectify_map(const double *K, const double *D, int n_dist, const double *R, const double *P, int width,
+                                       int height, float *map_x, float *map_y);
+
 /* measurement utility: sustained 32-bit POPC throughput of the device (ops/s), the denominator of the matching
  * roofline; runs a dependent-free popc microkernel for a few milliseconds. */
 int orbb200_popc_peak(int device, double *popc32_per_s);

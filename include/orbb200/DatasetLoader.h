@@ -59,6 +59,25 @@ inline void LoadImagesKITTI(const std::string &strPathToSequence, std::vector<st
     }
 }
 
+/* Examples/Stereo/stereo_euroc.cc:192-215: one timestamp (integer nanoseconds) per line of strPathTimes; the images are
+ * <left dir>/<stamp>.png and <right dir>/<stamp>.png, the time is stamp / 1e9 */
+inline void LoadImagesEuRoC(const std::string &strPathLeft, const std::string &strPathRight, const std::string &strPathTimes,
+                            std::vector<std::string> &vstrImageLeft, std::vector<std::string> &vstrImageRight, std::vector<double> &vTimeStamps)
+{
+    std::ifstream fTimes(strPathTimes.c_str());
+    std::string s;
+    while (std::getline(fTimes, s)) {
+        if (!s.empty() && s[s.size() - 1] == '\r') s.erase(s.size() - 1);
+        if (s.empty()) continue;
+        vstrImageLeft.push_back(strPathLeft + "/" + s + ".png");
+        vstrImageRight.push_back(strPathRight + "/" + s + ".png");
+        std::stringstream ss(s);
+        double t;
+        ss >> t;
+        vTimeStamps.push_back(t / 1e9);
+    }
+}
+
 inline void LoadImagesTUM(const std::string &strFile, std::vector<std::string> &vstrImageFilenames, std::vector<double> &vTimestamps)
 {
     std::ifstream f(strFile.c_str());

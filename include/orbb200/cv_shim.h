@@ -20,6 +20,8 @@
 #define CV_8UC1 0
 #define CV_32F 5
 #define CV_32FC1 5
+#define CV_64F 6
+#define CV_64FC1 6
 /* OpenCV's encoding: type = depth + ((channels - 1) << 3) */
 #define CV_8UC3 16
 #define CV_8UC4 24
@@ -116,7 +118,7 @@ public:
     const Mat &getMat() const { return *this; } /* so `_image.getMat()` style code keeps compiling */
 
 private:
-    static size_t esz(int type) { return (size_t)((type & 7) == CV_32F ? 4 : 1) * (size_t)((type >> 3) + 1); }
+    static size_t esz(int type) { return (size_t)((type & 7) == CV_64F ? 8 : (type & 7) == CV_32F ? 4 : 1) * (size_t)((type >> 3) + 1); }
     int type_;
     std::shared_ptr<unsigned char> store_;
 };

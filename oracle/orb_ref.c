@@ -1009,3 +1009,85 @@ int ref_stereo_match(const ref_keypoint *kL, const uint8_t *dL, int nL, const re
     free(rs); free(items); free(fill); free(vd);
     return nvalid;
 }
+
+/* ========================================================================= */
+/*            EuRoC prologue: stereo rectification (test infrastructure)      */
+/* ========================================================================= */
+/* cv::remap(src, dst, map1, map2, INTER_LINEAR) with CV_32FC1 maps, BORDER_CONSTANT 0 -- what Examples/Stereo/stereo_euroc.cc:
+ * 131-132 applies to both images of every frame.  OpenCV's fixed-point path: sx = cvRound(map1 * 32), sy likewise (INTER_BITS 5);
+ * integer part >> 5 saturated to short, fraction index (sy & 31) * 32 + (sx & 31) into a table of four 15-bit weights
+ * w = cvRound(float((1-fy)(1-fx)) * 32768) ... (initInterTab2D; the four always sum to 32768 for the linear kernel);
+ * dst = (sum w_i p_i + 16384) >> 15.  Pinned byte for byte against cv2.remap in tests/test_oracle_pin.py. */
+static short g_remap_tab[1024][4];
+static int g_remap_tab_ready = 0;
+const short *ref_remap_table(void)
+{
+    if (!g_remap_tab_ready) {
+        float t1[32][2];
+        for (int i = 0; i < 32; i++) {
+            const float x = (float)i * (1.0f / 32);
+            t1[i][0] = 1.0f - x;
+            t1[i][1] = x;
+        }
+        for (int i = 0; i < 32; i++)
+            for (int j = 0; j < 32; j++) {
+                const float f[4] = {t1[i][0] * t1[j][0], t1[i][0] * t1[j][1], t1[i][1] * t1[j][0], t1[i][1] * t1[j][1]};
+                for (int k = 0; k < 4; k++) g_remap_tab[i * 32 + j][k] = sat_short(cv_round_f(f[k] * 32768.f));
+            }
+        g_remap_tab_ready = 1;
+    }
+    return &g_remap_tab[0][0];
+}
+
+static inline int remap_px(const uint8_t *src, int sw, int sh, int sstride, int x, int y)
+{
+    return (x >= 0 && x < sw && y >= 0 && y < sh) ? src[(size_t)y * sstride + x] : 0;
+}
+
+void ref_remap_linear_u8(const uint8_t *src, int sw, int sh, int sstride, const float *mapx, const float *mapy, int dw, int dh,
+                         uint8_t *dst, int dstride)
+{
+    const short(*tab)[4] = (const short(*)[4])ref_remap_table();
+    for (int y = 0; y < dh; y++)
+        for (int x = 0; x < dw; x++) {
+            const int sx = cv_round_f(mapx[(size_t)y * dw + x] * 32.f), sy = cv_round_f(mapy[(size_t)y * dw + x] * 32.f);
+            int ix = sx >> 5, iy = sy >> 5;
+            ix = ix < -32768 ? -32768 : ix > 32767 ? 32767 : ix;
+            iy = iy < -32768 ? -32768 : iy > 32767 ? 32767 : iy;
+            const short *w = tab[(sy & 31) * 32 + (sx & 31)];
+            const int acc = remap_px(src, sw, sh, sstride, ix, iy) * w[0] + remap_px(src, sw, sh, sstride, ix + 1, iy) * w[1] +
+                            remap_px(src, sw, sh, sstride, ix, iy + 1) * w[2] + remap_px(src, sw, sh, sstride, ix + 1, iy + 1) * w[3];
+            const int v = (acc + 16384) >> 15;
+            dst[(size_t)y * dstride + x] = (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v);
+        }
+}
+
+/* cv::initUndistortRectifyMap(K, D, R, P(3x3), size, CV_32F, map1, map2) (stereo_euroc.cc:96-97), D = (k1, k2, p1, p2, k3):
+ * for every destination pixel the ray through the rectified camera is rotated back (inverse of P*R), distorted and projected
+ * with K.  Double arithmetic, one narrowing per map entry.  (OpenCV vectorises the row loop; entries may differ from it in the
+ * last bit of the double before the narrowing -- the test allows one float ulp on a handful of entries.) */
+void ref_init_undistort_rectify_map(const double *K, const double *D, const double *R, const double *P, int w, int h, float *mapx,
+                                    float *mapy)
+{
+    double M[9], ir[9];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) M[3 * i + j] = P[3 * i] * R[j] + P[3 * i + 1] * R[3 + j] + P[3 * i + 2] * R[6 + j];
+    const double det = M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
+    const double id = 1.0 / det;
+    ir[0] = (M[4] * M[8] - M[5] * M[7]) * id; ir[1] = (M[2] * M[7] - M[1] * M[8]) * id; ir[2] = (M[1] * M[5] - M[2] * M[4]) * id;
+    ir[3] = (M[5] * M[6] - M[3] * M[8]) * id; ir[4] = (M[0] * M[8] - M[2] * M[6]) * id; ir[5] = (M[2] * M[3] - M[0] * M[5]) * id;
+    ir[6] = (M[3] * M[7] - M[4] * M[6]) * id; ir[7] = (M[1] * M[6] - M[0] * M[7]) * id; ir[8] = (M[0] * M[4] - M[1] * M[3]) * id;
+    const double fx = K[0], fy = K[4], u0 = K[2], v0 = K[5];
+    const double k1 = D[0], k2 = D[1], p1 = D[2], p2 = D[3], k3 = D[4];
+    for (int i = 0; i < h; i++) {
+        double _x = i * ir[1] + ir[2], _y = i * ir[4] + ir[5], _w = i * ir[7] + ir[8];
+        for (int j = 0; j < w; j++, _x += ir[0], _y += ir[3], _w += ir[6]) {
+            const double ww = 1. / _w, x = _x * ww, y = _y * ww;
+            const double x2 = x * x, y2 = y * y, r2 = x2 + y2, _2xy = 2 * x * y;
+            const double kr = (1 + ((k3 * r2 + k2) * r2 + k1) * r2);
+            const double xd = x * kr + p1 * _2xy + p2 * (r2 + 2 * x2), yd = y * kr + p1 * (r2 + 2 * y2) + p2 * _2xy;
+            mapx[(size_t)i * w + j] = (float)(fx * xd + u0);
+            mapy[(size_t)i * w + j] = (float)(fy * yd + v0);
+        }
+    }
+}

@@ -247,3 +247,26 @@ def stereo_match(kL, dL, kR, dR, pyrL, pyrR, sf, isf, bf, b):
     n = lib().ref_stereo_match(_p(kL), _p(dL), len(kL), _p(kR), _p(dR), len(kR), PL, PR, _p(lw), _p(lh), _p(sf),
                                _p(isf), bf, b, _p(uR), _p(depth), _p(best))
     return uR, depth, best[:len(kL)], n
+
+
+def remap_linear(src, mapx, mapy):
+    """cv::remap(src, map1, map2, INTER_LINEAR), CV_32FC1 maps, BORDER_CONSTANT 0 (the EuRoC example's rectification)"""
+    src = np.ascontiguousarray(src, np.uint8)
+    mapx, mapy = np.ascontiguousarray(mapx, np.float32), np.ascontiguousarray(mapy, np.float32)
+    dh, dw = mapx.shape
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().ref_remap_linear_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(mapx), _p(mapy), dw, dh, _p(dst), dw)
+    return dst
+
+
+def init_undistort_rectify_map(K, D, R, P, w, h):
+    """cv::initUndistortRectifyMap(K, D = (k1, k2, p1, p2, k3), R, P[:3, :3], (w, h), CV_32F) -> (map1, map2)"""
+    K = np.ascontiguousarray(np.asarray(K, np.float64)[:3, :3].reshape(-1))
+    R = np.ascontiguousarray(np.asarray(R, np.float64)[:3, :3].reshape(-1))
+    P = np.ascontiguousarray(np.asarray(P, np.float64)[:3, :3].reshape(-1))
+    d = np.asarray(D, np.float64).reshape(-1)
+    D5 = np.zeros(5, np.float64)
+    D5[:min(5, len(d))] = d[:5]
+    mx, my = np.zeros((h, w), np.float32), np.zeros((h, w), np.float32)
+    lib().ref_init_undistort_rectify_map(_p(K), _p(D5), _p(R), _p(P), w, h, _p(mx), _p(my))
+    return mx, my

@@ -17,7 +17,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 TOP2_DTYPE = np.dtype([("best_dist", "<i4"), ("best_idx", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
 
 EXPORTS = [
-    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity", "orbb200_pyramid_layout", "orbb200_pyramid_download", "orbb200_pyramid_map", "orbb200_host_alloc", "orbb200_host_free", "orbb200_window_search_resident", "orbb200_extractor_outputs_device", "orbb200_device_alloc", "orbb200_device_free", "orbb200_copy_to_device", "orbb200_copy_to_host", "orbb200_copy_on_device", "orbb200_h2d_bytes_total", "orbb200_device_sync", "orbb200_bind_host_to_device", "orbb200_extractor_set_graph", "orbb200_extractor_set_octree_depth", "orbb200_extract_batch_begin", "orbb200_extract_stereo_batch_begin", "orbb200_extract_batch_wait",
+    "orbb200_extractor_create", "orbb200_extractor_destroy", "orbb200_level_tables", "orbb200_compute_level_tables", "orbb200_max_keypoints", "orbb200_max_keypoints_for_shape", "orbb200_last_capacity", "orbb200_pyramid_layout", "orbb200_pyramid_download", "orbb200_pyramid_map", "orbb200_host_alloc", "orbb200_host_free", "orbb200_window_search_resident", "orbb200_extractor_outputs_device", "orbb200_device_alloc", "orbb200_device_free", "orbb200_copy_to_device", "orbb200_copy_to_host", "orbb200_copy_on_device", "orbb200_h2d_bytes_total", "orbb200_device_sync", "orbb200_bind_host_to_device", "orbb200_extractor_set_graph", "orbb200_extractor_set_octree_depth", "orbb200_remap_create", "orbb200_remap_destroy", "orbb200_remap_batch", "orbb200_remap_batch_device", "orbb200_init_undistort_rectify_map", "orbb200_extract_batch_begin", "orbb200_extract_stereo_batch_begin", "orbb200_extract_batch_wait",
     "orbb200_extract", "orbb200_extract_batch", "orbb200_extract_batch_device", "orbb200_pyramid_level",
     "orbb200_extractor_stream", "orbb200_extractor_sync", "orbb200_extractor_set_profiling", "orbb200_extractor_set_pipeline",
     "orbb200_extractor_stage_ms", "orbb200_extractor_stage_ms_sum", "orbb200_extractor_last_launches", "orbb200_debug_candidates",
@@ -66,6 +66,12 @@ def lib():
     L.orbb200_extract_batch_begin.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, vp]
     L.orbb200_extract_stereo_batch_begin.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp, fp, fp, vp, vp, vp, vp]
     L.orbb200_extract_batch_wait.argtypes = [vp, ip]
+    L.orbb200_remap_create.argtypes = [vp, vp, vp, ip, ip, ip]
+    L.orbb200_remap_destroy.argtypes = [vp]
+    L.orbb200_remap_destroy.restype = None
+    L.orbb200_remap_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, ip]
+    L.orbb200_remap_batch_device.argtypes = [vp, vp, ip, ip, ip, ip, C.c_size_t, vp, ip, C.c_size_t, vp]
+    L.orbb200_init_undistort_rectify_map.argtypes = [vp, vp, ip, vp, vp, ip, ip, vp, vp]
     L.orbb200_extractor_set_graph.argtypes = [vp, ip]
     L.orbb200_extract.argtypes = [vp, vp, ip, ip, ip, vp, vp, ip, vp]
     L.orbb200_extract_batch.argtypes = [vp, vp, ip, ip, ip, ip, vp, vp, ip, vp]
@@ -633,3 +639,43 @@ def gather_top2_parts(part, group=None):
     out = torch.empty((world * part.shape[0],) + tuple(part.shape[1:]), dtype=part.dtype, device=part.device)
     dist.all_gather_into_tensor(out, part.contiguous(), group=group)  # concatenation along dim 0, rank order
     return out.view((world,) + tuple(part.shape))
+
+
+class Remap:
+    """cv::remap(src, M1, M2, INTER_LINEAR) of the EuRoC example (orbb200_remap_*): maps fixed at construction"""
+
+    def __init__(self, map_x, map_y, device=-1):
+        self.mx, self.my = np.ascontiguousarray(map_x, np.float32), np.ascontiguousarray(map_y, np.float32)
+        self.dh, self.dw = self.mx.shape
+        self.h = C.c_void_p()
+        check(lib().orbb200_remap_create(C.byref(self.h), _p(self.mx), _p(self.my), self.dw, self.dh, device))
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                lib().orbb200_remap_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: the module globals may be gone
+            pass
+
+    def __call__(self, images):
+        """images [batch][h][w] uint8 -> rectified [batch][dh][dw]"""
+        images = np.ascontiguousarray(images, np.uint8)
+        if images.ndim == 2:
+            return self(images[None])[0]
+        nb, sh, sw = images.shape
+        out = np.zeros((nb, self.dh, self.dw), np.uint8)
+        ip_ = (C.c_void_p * nb)(*[images[b].ctypes.data for b in range(nb)])
+        op_ = (C.c_void_p * nb)(*[out[b].ctypes.data for b in range(nb)])
+        check(lib().orbb200_remap_batch(self.h, ip_, nb, sw, sh, sw, op_, self.dw))
+        return out
+
+
+def init_undistort_rectify_map(K, D, R, P, w, h):
+    K = np.ascontiguousarray(np.asarray(K, np.float64)[:3, :3])
+    R = np.ascontiguousarray(np.asarray(R, np.float64)[:3, :3])
+    P = np.ascontiguousarray(np.asarray(P, np.float64)[:3, :3])
+    D = np.ascontiguousarray(np.asarray(D, np.float64).reshape(-1)[:5])
+    mx, my = np.zeros((h, w), np.float32), np.zeros((h, w), np.float32)
+    check(lib().orbb200_init_undistort_rectify_map(_p(K), _p(D), len(D), _p(R), _p(P), w, h, _p(mx), _p(my)))
+    return mx, my

@@ -9,9 +9,46 @@
 #include <vector>
 
 #include "orbb200/DatasetLoader.h"
+#include "orbb200/Rectify.h"
 
 int main(int argc, char **argv)
 {
+    // loader_test --euroc <left dir> <right dir> <times file> <calib.txt> <out.bin>: the EuRoC list (stereo_euroc.cc:192-215), and
+    // the first pair rectified as :96-97, 131-132 do (calib.txt: K D(5) R P(3x4) of the left then of the right camera, cols rows)
+    if (argc >= 7 && std::string(argv[1]) == "--euroc") {
+        std::vector<std::string> L, R;
+        std::vector<double> ts;
+        orbb200::LoadImagesEuRoC(argv[2], argv[3], argv[4], L, R, ts);
+        for (size_t i = 0; i < L.size(); i++) printf("euroc %.9f %s %s\n", ts[i], L[i].c_str(), R[i].c_str());
+        FILE *cf = fopen(argv[5], "r");
+        if (!cf) return 3;
+        double v[2][35];
+        int cols = 0, rows = 0;
+        for (int s = 0; s < 2; s++)
+            for (int i = 0; i < 35; i++)
+                if (fscanf(cf, "%lf", &v[s][i]) != 1) return 3;
+        if (fscanf(cf, "%d %d", &cols, &rows) != 2) return 3;
+        fclose(cf);
+        cv::Mat m[2][4];
+        for (int s = 0; s < 2; s++) {
+            m[s][0].create(3, 3, CV_64F); m[s][1].create(1, 5, CV_64F); m[s][2].create(3, 3, CV_64F); m[s][3].create(3, 4, CV_64F);
+            memcpy(m[s][0].data, &v[s][0], 72); memcpy(m[s][1].data, &v[s][9], 40); memcpy(m[s][2].data, &v[s][14], 72); memcpy(m[s][3].data, &v[s][23], 96);
+        }
+        orbb200::StereoRectifier rect(m[0][0], m[0][1], m[0][2], m[0][3], m[1][0], m[1][1], m[1][2], m[1][3], cols, rows);
+        if (!rect.ok() || L.empty()) return 4;
+        std::vector<unsigned char> pl, pr;
+        int w, h, ch, w2, h2, ch2;
+        std::string err;
+        if (!orbb200::ReadImage(L[0], pl, w, h, ch, &err) || !orbb200::ReadImage(R[0], pr, w2, h2, ch2, &err)) { printf("error %s\n", err.c_str()); return 3; }
+        cv::Mat imL(h, w, CV_8UC1, pl.data()), imR(h2, w2, CV_8UC1, pr.data()), rl, rr;
+        if (!rect(imL, imR, rl, rr)) return 4;
+        FILE *out = fopen(argv[6], "wb");
+        fwrite(rl.data, 1, (size_t)rl.rows * rl.cols, out);
+        fwrite(rr.data, 1, (size_t)rr.rows * rr.cols, out);
+        fclose(out);
+        printf("rectified %d %d\n", rl.cols, rl.rows);
+        return 0;
+    }
     if (argc < 4) return 2;
     const std::string dir = argv[1];
     const int ppb = atoi(argv[2]);
